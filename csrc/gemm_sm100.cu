@@ -1,0 +1,525 @@
+// gemm_sm100.cu — persistent, warp-specialised tcgen05 GEMM for sm_100a.
+//
+//   D[M,N] = epilogue( alpha * sum_k A(m,k) * B(n,k) )
+//
+// Design (B200-first, nothing here comes from the reference, which calls cuBLAS through nn.Linear:
+// hetseq/bert_modeling.py:166-172,352-354,388,424,515,526,544):
+//   * one CTA per SM, static round-robin tile scheduler over (m-block, n-block, k-split);
+//   * warp 0  : TMA producer — fills a ring of {A,B} shared-memory stages (128-byte swizzle);
+//   * warp 1  : allocates TMEM and issues tcgen05.mma (one elected lane), accumulating a 128xBN fp32
+//               tile in one of two TMEM accumulator slots so the epilogue of tile i overlaps tile i+1;
+//   * warps 2-5: epilogue — tcgen05.ld their 32-row quarter, apply alpha/bias/activation/aux in
+//               registers, stage 32x128B through swizzled smem, and TMA-store (or TMA reduce-add).
+//   * operands may be K-major or MN-major in global memory; MN-major tiles are fetched as 128-byte-wide
+//     slabs and described to the tensor core with the MN-major canonical layout, so forward, dgrad and
+//     wgrad all run through this kernel without any transpose pass.
+//   * kind::tf32 consumes fp32 storage directly (fp32/TF32 parity mode); kind::f16 consumes bf16.
+#include "common.h"
+#include "sm100_ptx.cuh"
+#include "../include/b200seq.h"
+
+#include <mutex>
+#include <unordered_map>
+#include <string>
+#include <cstring>
+
+namespace b200 {
+
+// ------------------------------------------------------------------------------------------------
+// device side
+// ------------------------------------------------------------------------------------------------
+struct GemmArgs {
+  int M, N, K;
+  int num_m, num_n, splits, kb_total, kb_per_split;
+  const void* bias;
+  const void* aux;
+  long long ldaux;
+  int act, aux_mode, accumulate, has_d2;
+  float alpha;
+};
+
+constexpr int kBM = 128;
+constexpr int kGemmThreads = 192;
+constexpr int kStageBufBytes = 4096;  // 32 rows x 128 B
+constexpr int kEpiBytes = 4 * 2 * kStageBufBytes;
+
+__device__ __forceinline__ float gelu_f(float x) { return 0.5f * x * (1.0f + erff(x * 0.70710678118654752f)); }
+__device__ __forceinline__ float dgelu_f(float x) {
+  const float cdf = 0.5f * (1.0f + erff(x * 0.70710678118654752f));
+  const float pdf = 0.3989422804014327f * __expf(-0.5f * x * x);
+  return cdf + x * pdf;
+}
+
+template <typename T>
+__device__ __forceinline__ float to_f(T v);
+template <>
+__device__ __forceinline__ float to_f<float>(float v) { return v; }
+template <>
+__device__ __forceinline__ float to_f<__nv_bfloat16>(__nv_bfloat16 v) { return __bfloat162float(v); }
+
+template <typename TIn, typename TOut, int BN, bool A_MN, bool B_MN, int STAGES>
+__global__ void __launch_bounds__(kGemmThreads, 1)
+gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
+                    const __grid_constant__ CUtensorMap tmD, const __grid_constant__ CUtensorMap tmD2,
+                    const GemmArgs args) {
+  constexpr int ES = sizeof(TIn);
+  constexpr int BK = 128 / ES;        // elements of K per stage (one 128 B swizzle span)
+  constexpr int UK = 32 / ES;         // K per tcgen05.mma (8 tf32 / 16 bf16)
+  constexpr int EA = 128 / ES;        // elements per 128 B along MN (MN-major slab width)
+  constexpr int A_BYTES = kBM * 128;
+  constexpr int B_BYTES = BN * 128;
+  constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
+  constexpr int SLAB_BYTES = BK * 128;
+  constexpr uint32_t ACC_STRIDE = (BN <= 64) ? 64 : (BN <= 128 ? 128 : 256);
+  constexpr uint32_t TMEM_COLS = 2 * ACC_STRIDE;
+  constexpr MmaKind KIND = (ES == 4) ? MmaKind::TF32 : MmaKind::F16;
+  constexpr uint32_t IDESC = make_idesc(ES == 4 ? 2u : 1u, A_MN, B_MN, kBM, BN);
+  constexpr int OS = sizeof(TOut);
+  constexpr int CW = 128 / OS;        // output columns per 128 B staging row (32 fp32 / 64 bf16)
+  static_assert(BN % CW == 0, "BN must be a multiple of the staging chunk width");
+
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* smem_stage = smem;                                  // STAGES * STAGE_BYTES
+  uint8_t* smem_epi = smem + STAGES * STAGE_BYTES;             // 4 warps x 2 x 4 KB
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem_epi + kEpiBytes);
+  uint64_t* full_bar = bars;
+  uint64_t* empty_bar = bars + STAGES;
+  uint64_t* tmem_full = bars + 2 * STAGES;
+  uint64_t* tmem_empty = bars + 2 * STAGES + 2;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * STAGES + 4);
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&tmA);
+    tma_prefetch_desc(&tmB);
+    tma_prefetch_desc(&tmD);
+    for (int s = 0; s < STAGES; ++s) {
+      mbar_init(&full_bar[s], 1);
+      mbar_init(&empty_bar[s], 1);
+    }
+    for (int a = 0; a < 2; ++a) {
+      mbar_init(&tmem_full[a], 1);
+      mbar_init(&tmem_empty[a], 4);
+    }
+    fence_barrier_init();
+  }
+  if (warp == 1) tmem_alloc<TMEM_COLS>(tmem_slot);
+  tcgen05_fence_before();
+  __syncthreads();
+  tcgen05_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  const int num_tiles = args.num_m * args.num_n * args.splits;
+
+  if (warp == 0) {
+    // ===================================== TMA producer =====================================
+    if (lane == 0) {
+      uint32_t it = 0;
+      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+        const int split = tile % args.splits;
+        const int rest = tile / args.splits;
+        const int n0 = (rest % args.num_n) * BN;
+        const int m0 = (rest / args.num_n) * kBM;
+        const int kb0 = split * args.kb_per_split;
+        const int kb1 = min(args.kb_total, kb0 + args.kb_per_split);
+        for (int kb = kb0; kb < kb1; ++kb, ++it) {
+          const uint32_t s = it % STAGES;
+          const uint32_t ph = (it / STAGES) & 1;
+          mbar_wait(&empty_bar[s], ph ^ 1);
+          mbar_arrive_expect_tx(&full_bar[s], STAGE_BYTES);
+          uint8_t* sA = smem_stage + s * STAGE_BYTES;
+          uint8_t* sB = sA + A_BYTES;
+          const int k0 = kb * BK;
+          if constexpr (!A_MN) {
+            tma_load_2d(sA, &tmA, &full_bar[s], k0, m0);
+          } else {
+#pragma unroll
+            for (int sl = 0; sl < kBM / EA; ++sl) tma_load_2d(sA + sl * SLAB_BYTES, &tmA, &full_bar[s], m0 + sl * EA, k0);
+          }
+          if constexpr (!B_MN) {
+            tma_load_2d(sB, &tmB, &full_bar[s], k0, n0);
+          } else {
+#pragma unroll
+            for (int sl = 0; sl < BN / EA; ++sl) tma_load_2d(sB + sl * SLAB_BYTES, &tmB, &full_bar[s], n0 + sl * EA, k0);
+          }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ===================================== MMA issuer =======================================
+    if (lane == 0) {
+      uint32_t it = 0;
+      uint32_t tcount = 0;
+      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++tcount) {
+        const int split = tile % args.splits;
+        const int kb0 = split * args.kb_per_split;
+        const int kb1 = min(args.kb_total, kb0 + args.kb_per_split);
+        const uint32_t acc = tcount & 1;
+        mbar_wait(&tmem_empty[acc], ((tcount >> 1) & 1) ^ 1);
+        tcgen05_fence_after();
+        const uint32_t d_tmem = tmem_base + acc * ACC_STRIDE;
+        for (int kb = kb0; kb < kb1; ++kb, ++it) {
+          const uint32_t s = it % STAGES;
+          const uint32_t ph = (it / STAGES) & 1;
+          mbar_wait(&full_bar[s], ph);
+          tcgen05_fence_after();
+          const uint32_t a_addr = smem_u32(smem_stage + s * STAGE_BYTES);
+          const uint32_t b_addr = a_addr + A_BYTES;
+          // MN-major fp32 tiles use the 32-byte-atom swizzle (layout type 1, 4-row atoms)
+          constexpr uint32_t MN_SBO = (ES == 4) ? 512 : 1024;
+          constexpr uint32_t MN_LT = (ES == 4) ? 1 : 2;
+          const uint64_t a_desc = A_MN ? make_smem_desc_sw128(a_addr, SLAB_BYTES, MN_SBO, MN_LT)
+                                       : make_smem_desc_sw128(a_addr, 16, 1024);
+          const uint64_t b_desc = B_MN ? make_smem_desc_sw128(b_addr, SLAB_BYTES, MN_SBO, MN_LT)
+                                       : make_smem_desc_sw128(b_addr, 16, 1024);
+#pragma unroll
+          for (int j = 0; j < BK / UK; ++j) {
+            // advance inside the stage: K-major -> 32 B along the swizzled row; MN-major -> UK rows of 128 B
+            const uint64_t a_off = A_MN ? (uint64_t)((j * UK * 128) >> 4) : (uint64_t)((j * 32) >> 4);
+            const uint64_t b_off = B_MN ? (uint64_t)((j * UK * 128) >> 4) : (uint64_t)((j * 32) >> 4);
+            tcgen05_mma_ss<KIND>(d_tmem, a_desc + a_off, b_desc + b_off, IDESC, (kb > kb0 || j > 0) ? 1u : 0u);
+          }
+          tcgen05_commit(&empty_bar[s]);   // frees the smem stage once these MMAs have read it
+        }
+        tcgen05_commit(&tmem_full[acc]);   // accumulator complete -> epilogue
+      }
+    }
+  } else {
+    // ===================================== epilogue =========================================
+    const int ew = warp - 2;               // staging-buffer owner index 0..3
+    const int q = warp & 3;                // TMEM lane quarter this warp may read
+    uint8_t* stg = smem_epi + ew * 2 * kStageBufBytes;
+    uint32_t ev = 0;                       // store-event counter (ring of 2 staging buffers)
+    uint32_t tcount = 0;
+    const TOut* bias = reinterpret_cast<const TOut*>(args.bias);
+    const TOut* aux = reinterpret_cast<const TOut*>(args.aux);
+    const bool vec_ok = (args.N % (16 / OS)) == 0;
+
+    for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++tcount) {
+      const int split = tile % args.splits;
+      const int rest = tile / args.splits;
+      const int n0 = (rest % args.num_n) * BN;
+      const int m0 = (rest / args.num_n) * kBM;
+      const uint32_t acc = tcount & 1;
+      mbar_wait(&tmem_full[acc], (tcount >> 1) & 1);
+      tcgen05_fence_after();
+      const int row = m0 + q * 32 + lane;
+      const bool add_bias = (bias != nullptr) && (split == 0);
+
+#pragma unroll 1
+      for (int c = 0; c < BN / CW; ++c) {
+        const int nc = n0 + c * CW;
+        if (nc >= args.N) break;           // warp-uniform: whole chunk is out of range
+        float v[CW];
+#pragma unroll
+        for (int h = 0; h < CW / 32; ++h) {
+          uint32_t r[32];
+          tmem_ld_32x32(tmem_base + ((uint32_t)(q * 32) << 16) + acc * ACC_STRIDE + c * CW + h * 32, r);
+          tmem_ld_wait();
+#pragma unroll
+          for (int j = 0; j < 32; ++j) v[h * 32 + j] = __uint_as_float(r[j]) * args.alpha;
+        }
+        if (add_bias) {
+          if (vec_ok) {
+#pragma unroll
+            for (int j = 0; j < CW; j += 16 / OS) {
+              if (nc + j < args.N) {
+                const uint4 u = __ldg(reinterpret_cast<const uint4*>(bias + nc + j));
+                const TOut* b = reinterpret_cast<const TOut*>(&u);
+#pragma unroll
+                for (int e = 0; e < 16 / OS; ++e) v[j + e] += to_f<TOut>(b[e]);
+              }
+            }
+          } else {
+#pragma unroll
+            for (int j = 0; j < CW; ++j)
+              if (nc + j < args.N) v[j] += to_f<TOut>(__ldg(bias + nc + j));
+          }
+        }
+
+        auto stage_and_store = [&](const CUtensorMap* tm, bool reduce) {
+          uint8_t* buf = stg + (ev & 1) * kStageBufBytes;
+          if (lane == 0) tma_store_wait_read<1>();   // the store that last used this buffer has drained
+          __syncwarp();
+          uint8_t* rowp = buf + lane * 128;
+#pragma unroll
+          for (int i = 0; i < 8; ++i) {
+            uint4 u;
+            if constexpr (OS == 4) {
+              u.x = __float_as_uint(v[4 * i + 0]);
+              u.y = __float_as_uint(v[4 * i + 1]);
+              u.z = __float_as_uint(v[4 * i + 2]);
+              u.w = __float_as_uint(v[4 * i + 3]);
+            } else {
+              __nv_bfloat162 p0 = __floats2bfloat162_rn(v[8 * i + 0], v[8 * i + 1]);
+              __nv_bfloat162 p1 = __floats2bfloat162_rn(v[8 * i + 2], v[8 * i + 3]);
+              __nv_bfloat162 p2 = __floats2bfloat162_rn(v[8 * i + 4], v[8 * i + 5]);
+              __nv_bfloat162 p3 = __floats2bfloat162_rn(v[8 * i + 6], v[8 * i + 7]);
+              u.x = *reinterpret_cast<uint32_t*>(&p0);
+              u.y = *reinterpret_cast<uint32_t*>(&p1);
+              u.z = *reinterpret_cast<uint32_t*>(&p2);
+              u.w = *reinterpret_cast<uint32_t*>(&p3);
+            }
+            *reinterpret_cast<uint4*>(rowp + ((i ^ (lane & 7)) << 4)) = u;
+          }
+          fence_proxy_async_smem();
+          __syncwarp();
+          if (lane == 0) {
+            if (reduce) tma_reduce_add_2d(tm, buf, nc, m0 + q * 32);
+            else tma_store_2d(tm, buf, nc, m0 + q * 32);
+            tma_store_commit();
+          }
+          ++ev;
+        };
+
+        if (args.has_d2) stage_and_store(&tmD2, false);
+
+        if (args.act == B200_ACT_GELU) {
+#pragma unroll
+          for (int j = 0; j < CW; ++j) v[j] = gelu_f(v[j]);
+        } else if (args.act == B200_ACT_TANH) {
+#pragma unroll
+          for (int j = 0; j < CW; ++j) v[j] = tanhf(v[j]);
+        }
+
+        if (args.aux_mode != B200_AUX_NONE && row < args.M) {
+          const TOut* arow = aux + (long long)row * args.ldaux + nc;
+#pragma unroll
+          for (int j = 0; j < CW; j += 16 / OS) {
+            if (nc + j < args.N) {
+              const uint4 u = __ldg(reinterpret_cast<const uint4*>(arow + j));
+              const TOut* a = reinterpret_cast<const TOut*>(&u);
+#pragma unroll
+              for (int e = 0; e < 16 / OS; ++e) {
+                const float x = to_f<TOut>(a[e]);
+                if (args.aux_mode == B200_AUX_ADD) v[j + e] += x;
+                else if (args.aux_mode == B200_AUX_MUL_DGELU) v[j + e] *= dgelu_f(x);
+                else v[j + e] *= (1.0f - x * x);
+              }
+            }
+          }
+        }
+        stage_and_store(&tmD, args.accumulate != 0);
+      }
+      // all TMEM reads of this accumulator slot are done -> hand it back to the MMA warp
+      tcgen05_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&tmem_empty[acc]);
+    }
+    if (lane == 0) tma_store_wait_read<0>();
+    __syncwarp();
+  }
+
+  tcgen05_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    tcgen05_fence_after();
+    tmem_dealloc<TMEM_COLS>(tmem_base);
+  }
+}
+
+// ------------------------------------------------------------------------------------------------
+// host side: tensor maps
+// ------------------------------------------------------------------------------------------------
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+static EncodeTiledFn get_encode_fn() {
+  static EncodeTiledFn fn = nullptr;
+  static std::once_flag once;
+  std::call_once(once, [] {
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult qres;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &qres) == cudaSuccess &&
+        qres == cudaDriverEntryPointSuccess)
+      fn = reinterpret_cast<EncodeTiledFn>(p);
+  });
+  return fn;
+}
+
+// 2-D row-major tensor [rows][cols] with pitch `ld` elements; box = box_cols x box_rows; 128 B swizzle.
+int make_tmap_2d(CUtensorMap* out, const void* ptr, int elem_bytes, bool is_bf16, long long rows, long long cols,
+                 long long ld, int box_cols, int box_rows, bool atom32 = false) {
+  EncodeTiledFn fn = get_encode_fn();
+  if (!fn) return fail(B200_ERR_DRIVER, "cuTensorMapEncodeTiled entry point unavailable");
+  if ((reinterpret_cast<uintptr_t>(ptr) & 15) != 0) return fail(B200_ERR_ARG, "TMA base pointer must be 16-byte aligned");
+  if (((ld * elem_bytes) & 15) != 0) return fail(B200_ERR_ARG, "TMA row pitch (%lld B) must be a multiple of 16", ld * elem_bytes);
+  if (box_cols * elem_bytes > 128 || box_rows > 256) return fail(B200_ERR_ARG, "TMA box too large");
+  cuuint64_t dims[2] = {(cuuint64_t)cols, (cuuint64_t)rows};
+  cuuint64_t strides[1] = {(cuuint64_t)(ld * elem_bytes)};
+  cuuint32_t box[2] = {(cuuint32_t)box_cols, (cuuint32_t)box_rows};
+  cuuint32_t estr[2] = {1, 1};
+  CUtensorMapDataType dt = elem_bytes == 4 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32
+                                           : (is_bf16 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT16);
+  CUresult r = fn(out, dt, 2, const_cast<void*>(ptr), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                  atom32 ? CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B : CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) return fail(B200_ERR_DRIVER, "cuTensorMapEncodeTiled failed (%d) rows=%lld cols=%lld ld=%lld box=%dx%d",
+                                     (int)r, rows, cols, ld, box_cols, box_rows);
+  return 0;
+}
+
+// ------------------------------------------------------------------------------------------------
+// host side: dispatch
+// ------------------------------------------------------------------------------------------------
+template <int BN>
+constexpr int stages_for() {
+  // 227 KB usable; keep 32 KB for the epilogue staging ring, ~2 KB for alignment slack + barriers.
+  constexpr int stage = kBM * 128 + BN * 128;
+  constexpr int avail = 232448 - kEpiBytes - 2048;
+  constexpr int s = avail / stage;
+  return s > 8 ? 8 : s;
+}
+
+template <typename TIn, typename TOut, int BN, bool A_MN, bool B_MN>
+static int launch_gemm(const CUtensorMap& tA, const CUtensorMap& tB, const CUtensorMap& tD, const CUtensorMap& tD2,
+                       const GemmArgs& args, cudaStream_t stream) {
+  constexpr int STAGES = stages_for<BN>();
+  constexpr int smem = STAGES * (kBM * 128 + BN * 128) + kEpiBytes + 1024 /*align*/ + (2 * STAGES + 4) * 8 + 16;
+  auto kern = gemm_tcgen05_kernel<TIn, TOut, BN, A_MN, B_MN, STAGES>;
+  static bool attr_set = false;
+  if (!attr_set) {
+    B200_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    attr_set = true;
+  }
+  const int tiles = args.num_m * args.num_n * args.splits;
+  const int grid = tiles < num_sms() ? tiles : num_sms();
+  kern<<<grid, kGemmThreads, smem, stream>>>(tA, tB, tD, tD2, args);
+  B200_LAUNCHED("gemm_tcgen05_kernel");
+  return 0;
+}
+
+template <typename TIn, typename TOut, int BN>
+static int dispatch_major(bool a_mn, bool b_mn, const CUtensorMap& tA, const CUtensorMap& tB, const CUtensorMap& tD,
+                          const CUtensorMap& tD2, const GemmArgs& args, cudaStream_t stream) {
+  if (!a_mn && !b_mn) return launch_gemm<TIn, TOut, BN, false, false>(tA, tB, tD, tD2, args, stream);
+  if (!a_mn && b_mn) return launch_gemm<TIn, TOut, BN, false, true>(tA, tB, tD, tD2, args, stream);
+  if (a_mn && b_mn) return launch_gemm<TIn, TOut, BN, true, true>(tA, tB, tD, tD2, args, stream);
+  return launch_gemm<TIn, TOut, BN, true, false>(tA, tB, tD, tD2, args, stream);
+}
+
+template <typename TIn, typename TOut>
+static int dispatch_bn(int bn, bool a_mn, bool b_mn, const CUtensorMap& tA, const CUtensorMap& tB, const CUtensorMap& tD,
+                       const CUtensorMap& tD2, const GemmArgs& args, cudaStream_t stream) {
+  switch (bn) {
+    case 64: return dispatch_major<TIn, TOut, 64>(a_mn, b_mn, tA, tB, tD, tD2, args, stream);
+    case 128: return dispatch_major<TIn, TOut, 128>(a_mn, b_mn, tA, tB, tD, tD2, args, stream);
+    case 192: return dispatch_major<TIn, TOut, 192>(a_mn, b_mn, tA, tB, tD, tD2, args, stream);
+    case 256: return dispatch_major<TIn, TOut, 256>(a_mn, b_mn, tA, tB, tD, tD2, args, stream);
+  }
+  return fail(B200_ERR_ARG, "unsupported BN %d", bn);
+}
+
+// Pick the N tile: minimise (waves x tile cost); BN=64 re-reads A from smem at twice the tensor-core rate,
+// so it carries a penalty and is only chosen for very small problems.
+static int choose_bn(int M, int N, int splits) {
+  const int sms = num_sms();
+  const int cands[4] = {256, 192, 128, 64};
+  double best = 1e30;
+  int best_bn = 128;
+  const int num_m = (M + kBM - 1) / kBM;
+  for (int i = 0; i < 4; ++i) {
+    const int bn = cands[i];
+    const int num_n = (N + bn - 1) / bn;
+    const long long tiles = (long long)num_m * num_n * splits;
+    const long long waves = (tiles + sms - 1) / sms;
+    double cost = (double)waves * (bn == 64 ? 96.0 : (double)bn) + 8.0 * waves;  // + per-tile fixed overhead
+    if (cost < best - 1e-9) {
+      best = cost;
+      best_bn = bn;
+    }
+  }
+  return best_bn;
+}
+
+static int gemm_impl(const b200_gemm_desc* d, cudaStream_t stream) {
+  if (!d || !d->A || !d->B || !d->D) return fail(B200_ERR_ARG, "gemm: null pointer");
+  if (d->M <= 0 || d->N <= 0 || d->K <= 0) return fail(B200_ERR_ARG, "gemm: bad shape %dx%dx%d", d->M, d->N, d->K);
+  const bool in_bf16 = d->dtype != B200_F32_TF32;
+  const bool out_bf16 = d->dtype == B200_BF16;
+  const int es = in_bf16 ? 2 : 4;
+  const int os = out_bf16 ? 2 : 4;
+  if (d->accumulate && out_bf16) return fail(B200_ERR_UNSUPPORTED, "gemm: accumulate needs fp32 output");
+  if (d->aux_mode != B200_AUX_NONE) {
+    if (!d->aux) return fail(B200_ERR_ARG, "gemm: aux_mode set but aux is null");
+    if ((d->N % (16 / os)) != 0 || ((d->ldaux * os) & 15) != 0 || (reinterpret_cast<uintptr_t>(d->aux) & 15))
+      return fail(B200_ERR_ARG, "gemm: aux needs N and pitch multiple of 16 bytes and an aligned base");
+  }
+  if (d->bias && (d->N % (16 / os)) == 0 && (reinterpret_cast<uintptr_t>(d->bias) & 15))
+    return fail(B200_ERR_ARG, "gemm: bias must be 16-byte aligned");
+
+  const int BK = 128 / es;
+  const int EA = 128 / es;
+  const int kb_total = (d->K + BK - 1) / BK;
+  const int num_m = (d->M + kBM - 1) / kBM;
+
+  int splits = 1;
+  if (d->accumulate) {
+    splits = d->splits;
+    if (splits <= 0) {
+      // auto split-K: fill the machine when the output has few tiles, keep >= 8 k-blocks per split
+      const int base_bn = d->bn > 0 ? d->bn : 128;
+      const long long tiles = (long long)num_m * ((d->N + base_bn - 1) / base_bn);
+      splits = (int)(num_sms() / (tiles > 0 ? tiles : 1));
+      if (splits < 1) splits = 1;
+      const int max_by_k = kb_total / 8 > 0 ? kb_total / 8 : 1;
+      if (splits > max_by_k) splits = max_by_k;
+      if (splits > 16) splits = 16;
+    }
+  }
+  int kb_per_split = (kb_total + splits - 1) / splits;
+  splits = (kb_total + kb_per_split - 1) / kb_per_split;  // no empty split
+
+  const int bn = d->bn > 0 ? d->bn : choose_bn(d->M, d->N, splits);
+  if (bn != 64 && bn != 128 && bn != 192 && bn != 256) return fail(B200_ERR_ARG, "gemm: bn must be 64/128/192/256");
+
+  CUtensorMap tA, tB, tD, tD2;
+  int rc;
+  if (!d->a_mn) rc = make_tmap_2d(&tA, d->A, es, in_bf16, d->M, d->K, d->lda, BK, kBM);
+  else rc = make_tmap_2d(&tA, d->A, es, in_bf16, d->K, d->M, d->lda, EA, BK, es == 4);
+  if (rc) return rc;
+  if (!d->b_mn) rc = make_tmap_2d(&tB, d->B, es, in_bf16, d->N, d->K, d->ldb, BK, bn);
+  else rc = make_tmap_2d(&tB, d->B, es, in_bf16, d->K, d->N, d->ldb, EA, BK, es == 4);
+  if (rc) return rc;
+  const int CW = 128 / os;
+  rc = make_tmap_2d(&tD, d->D, os, out_bf16, d->M, d->N, d->ldd, CW, 32);
+  if (rc) return rc;
+  if (d->D2) {
+    rc = make_tmap_2d(&tD2, d->D2, os, out_bf16, d->M, d->N, d->ldd, CW, 32);
+    if (rc) return rc;
+  } else {
+    tD2 = tD;
+  }
+
+  GemmArgs a;
+  a.M = d->M; a.N = d->N; a.K = d->K;
+  a.num_m = num_m;
+  a.num_n = (d->N + bn - 1) / bn;
+  a.splits = splits;
+  a.kb_total = kb_total;
+  a.kb_per_split = kb_per_split;
+  a.bias = d->bias;
+  a.aux = d->aux;
+  a.ldaux = d->ldaux;
+  a.act = d->act;
+  a.aux_mode = d->aux_mode;
+  a.accumulate = d->accumulate;
+  a.has_d2 = d->D2 != nullptr;
+  a.alpha = d->alpha;
+
+  switch (d->dtype) {
+    case B200_F32_TF32: return dispatch_bn<float, float>(bn, d->a_mn, d->b_mn, tA, tB, tD, tD2, a, stream);
+    case B200_BF16: return dispatch_bn<__nv_bfloat16, __nv_bfloat16>(bn, d->a_mn, d->b_mn, tA, tB, tD, tD2, a, stream);
+    case B200_BF16_F32OUT: return dispatch_bn<__nv_bfloat16, float>(bn, d->a_mn, d->b_mn, tA, tB, tD, tD2, a, stream);
+  }
+  return fail(B200_ERR_ARG, "gemm: unknown dtype %d", d->dtype);
+}
+
+}  // namespace b200
+
+extern "C" int b200_gemm(const b200_gemm_desc* d, void* stream) {
+  return b200::gemm_impl(d, reinterpret_cast<cudaStream_t>(stream));
+}

@@ -1,0 +1,95 @@
+"""Python front-end of the tcgen05 GEMM (``csrc/gemm_sm100.cu``).
+
+``gemm(a, b, ...)`` computes ``D[M,N] = epilogue(alpha * A @ B^T-like)`` where each operand may be
+stored K-major or MN-major; see ``include/b200seq.h``.  Replaces every cuBLAS call behind ``nn.Linear``
+in the reference (``hetseq/bert_modeling.py:166-172,352-354,388,424,515,526,544``).
+"""
+from __future__ import annotations
+
+import ctypes
+from typing import Optional
+
+import torch
+
+from . import native
+
+_DT = {torch.float32: 4, torch.bfloat16: 2}
+
+
+def _stream_ptr() -> int:
+    return torch.cuda.current_stream().cuda_stream
+
+
+def _rowmajor_2d(t: torch.Tensor, name: str):
+    if t.dim() != 2 or t.stride(1) != 1:
+        raise ValueError(f"{name}: expected a 2-D tensor with unit inner stride, got shape={tuple(t.shape)} stride={t.stride()}")
+    return t.shape[0], t.shape[1], t.stride(0)
+
+
+def gemm(a: torch.Tensor, b: torch.Tensor, *, a_mn: bool = False, b_mn: bool = False,
+         out: Optional[torch.Tensor] = None, out_dtype: Optional[torch.dtype] = None,
+         bias: Optional[torch.Tensor] = None, act: int = native.ACT_NONE,
+         aux: Optional[torch.Tensor] = None, aux_mode: int = native.AUX_NONE,
+         preact_out: Optional[torch.Tensor] = None, accumulate: bool = False, alpha: float = 1.0,
+         bn: int = 0, splits: int = 0) -> torch.Tensor:
+    """D = epilogue(alpha * sum_k A(m,k) B(n,k)).
+
+    a: [M,K] (a_mn=False) or [K,M] (a_mn=True);  b: [N,K] (b_mn=False) or [K,N] (b_mn=True).
+    fp32 operands run on kind::tf32, bf16 operands on kind::f16; output dtype defaults to the operand
+    dtype (bf16 operands may request fp32 output, used for weight gradients).
+    """
+    if a.dtype != b.dtype or a.dtype not in _DT:
+        raise ValueError(f"gemm: unsupported operand dtypes {a.dtype}/{b.dtype}")
+    ra, ca, lda = _rowmajor_2d(a, "a")
+    rb, cb, ldb = _rowmajor_2d(b, "b")
+    M, K = (ca, ra) if a_mn else (ra, ca)
+    N, Kb = (cb, rb) if b_mn else (rb, cb)
+    if K != Kb:
+        raise ValueError(f"gemm: reduction mismatch {K} vs {Kb}")
+    odt = out_dtype or (out.dtype if out is not None else a.dtype)
+    if a.dtype == torch.float32:
+        if odt != torch.float32:
+            raise ValueError("gemm: fp32 operands produce fp32 output")
+        dt = native.F32_TF32
+    else:
+        dt = native.BF16 if odt == torch.bfloat16 else native.BF16_F32OUT
+    if out is None:
+        if accumulate:
+            raise ValueError("gemm: accumulate=True needs an explicit out tensor")
+        pad = 16 // _DT[odt]
+        ldd = (N + pad - 1) // pad * pad
+        out = torch.empty((M, ldd), dtype=odt, device=a.device)[:, :N] if ldd != N else torch.empty((M, N), dtype=odt, device=a.device)
+    ro, co, ldd = _rowmajor_2d(out, "out")
+    if (ro, co) != (M, N) or out.dtype != odt:
+        raise ValueError(f"gemm: out has shape {tuple(out.shape)}/{out.dtype}, expected {(M, N)}/{odt}")
+    d = native.GemmDesc()
+    d.dtype, d.M, d.N, d.K = dt, M, N, K
+    d.A, d.lda, d.a_mn = a.data_ptr(), lda, int(a_mn)
+    d.B, d.ldb, d.b_mn = b.data_ptr(), ldb, int(b_mn)
+    d.D, d.ldd = out.data_ptr(), ldd
+    if preact_out is not None:
+        rp, cp, ldp = _rowmajor_2d(preact_out, "preact_out")
+        if (rp, cp, ldp) != (M, N, ldd) or preact_out.dtype != odt:
+            raise ValueError("gemm: preact_out must match out in shape, pitch and dtype")
+        d.D2 = preact_out.data_ptr()
+    else:
+        d.D2 = None
+    if bias is not None:
+        if bias.dtype != odt or bias.numel() != N or not bias.is_contiguous():
+            raise ValueError("gemm: bias must be a contiguous [N] tensor of the output dtype")
+        d.bias = bias.data_ptr()
+    else:
+        d.bias = None
+    if aux is not None:
+        rx, cx, ldx = _rowmajor_2d(aux, "aux")
+        if (rx, cx) != (M, N) or aux.dtype != odt:
+            raise ValueError("gemm: aux must be [M,N] of the output dtype")
+        d.aux, d.ldaux = aux.data_ptr(), ldx
+    else:
+        d.aux, d.ldaux = None, 0
+        if aux_mode != native.AUX_NONE:
+            raise ValueError("gemm: aux_mode without aux")
+    d.act, d.aux_mode, d.accumulate, d.alpha = act, aux_mode, int(accumulate), float(alpha)
+    d.bn, d.splits = bn, splits
+    native.check(native.cuda_lib().b200_gemm(ctypes.byref(d), _stream_ptr()), "b200_gemm")
+    return out

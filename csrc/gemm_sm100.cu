@@ -31,6 +31,7 @@ namespace b200 {
 struct GemmArgs {
   int M, N, K;
   int num_m, num_n, splits, kb_total, kb_per_split;
+  int nb0, nbatch;   // batch = b1 * nb0 + b0 (e.g. b0 = head, b1 = sequence)
   const void* bias;
   const void* aux;
   long long ldaux;
@@ -112,7 +113,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
   tcgen05_fence_after();
   const uint32_t tmem_base = *tmem_slot;
 
-  const int num_tiles = args.num_m * args.num_n * args.splits;
+  const int num_tiles = args.nbatch * args.num_m * args.num_n * args.splits;
 
   if (warp == 0) {
     // ===================================== TMA producer =====================================
@@ -120,9 +121,12 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
       uint32_t it = 0;
       for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
         const int split = tile % args.splits;
-        const int rest = tile / args.splits;
+        int rest = tile / args.splits;
         const int n0 = (rest % args.num_n) * BN;
-        const int m0 = (rest / args.num_n) * kBM;
+        rest /= args.num_n;
+        const int m0 = (rest % args.num_m) * kBM;
+        const int bt = rest / args.num_m;
+        const int b0 = bt % args.nb0, b1 = bt / args.nb0;
         const int kb0 = split * args.kb_per_split;
         const int kb1 = min(args.kb_total, kb0 + args.kb_per_split);
         for (int kb = kb0; kb < kb1; ++kb, ++it) {
@@ -134,16 +138,16 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
           uint8_t* sB = sA + A_BYTES;
           const int k0 = kb * BK;
           if constexpr (!A_MN) {
-            tma_load_2d(sA, &tmA, &full_bar[s], k0, m0);
+            tma_load_4d(sA, &tmA, &full_bar[s], k0, m0, b0, b1);
           } else {
 #pragma unroll
-            for (int sl = 0; sl < kBM / EA; ++sl) tma_load_2d(sA + sl * SLAB_BYTES, &tmA, &full_bar[s], m0 + sl * EA, k0);
+            for (int sl = 0; sl < kBM / EA; ++sl) tma_load_4d(sA + sl * SLAB_BYTES, &tmA, &full_bar[s], m0 + sl * EA, k0, b0, b1);
           }
           if constexpr (!B_MN) {
-            tma_load_2d(sB, &tmB, &full_bar[s], k0, n0);
+            tma_load_4d(sB, &tmB, &full_bar[s], k0, n0, b0, b1);
           } else {
 #pragma unroll
-            for (int sl = 0; sl < BN / EA; ++sl) tma_load_2d(sB + sl * SLAB_BYTES, &tmB, &full_bar[s], n0 + sl * EA, k0);
+            for (int sl = 0; sl < BN / EA; ++sl) tma_load_4d(sB + sl * SLAB_BYTES, &tmB, &full_bar[s], n0 + sl * EA, k0, b0, b1);
           }
         }
       }
@@ -200,9 +204,12 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
 
     for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++tcount) {
       const int split = tile % args.splits;
-      const int rest = tile / args.splits;
+      int rest = tile / args.splits;
       const int n0 = (rest % args.num_n) * BN;
-      const int m0 = (rest / args.num_n) * kBM;
+      rest /= args.num_n;
+      const int m0 = (rest % args.num_m) * kBM;
+      const int bt = rest / args.num_m;
+      const int b0 = bt % args.nb0, b1 = bt / args.nb0;
       const uint32_t acc = tcount & 1;
       mbar_wait(&tmem_full[acc], (tcount >> 1) & 1);
       tcgen05_fence_after();
@@ -212,7 +219,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
 #pragma unroll 1
       for (int c = 0; c < BN / CW; ++c) {
         const int nc = n0 + c * CW;
-        if (nc >= args.N) break;           // warp-uniform: whole chunk is out of range
+        if (nc >= args.N || m0 + q * 32 >= args.M) break;   // warp-uniform: nothing of this chunk is in range
         float v[CW];
 #pragma unroll
         for (int h = 0; h < CW / 32; ++h) {
@@ -268,8 +275,8 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
           fence_proxy_async_smem();
           __syncwarp();
           if (lane == 0) {
-            if (reduce) tma_reduce_add_2d(tm, buf, nc, m0 + q * 32);
-            else tma_store_2d(tm, buf, nc, m0 + q * 32);
+            if (reduce) tma_reduce_add_4d(tm, buf, nc, m0 + q * 32, b0, b1);
+            else tma_store_4d(tm, buf, nc, m0 + q * 32, b0, b1);
             tma_store_commit();
           }
           ++ev;
@@ -342,20 +349,26 @@ static EncodeTiledFn get_encode_fn() {
 }
 
 // 2-D row-major tensor [rows][cols] with pitch `ld` elements; box = box_cols x box_rows; 128 B swizzle.
-int make_tmap_2d(CUtensorMap* out, const void* ptr, int elem_bytes, bool is_bf16, long long rows, long long cols,
-                 long long ld, int box_cols, int box_rows, bool atom32 = false) {
+int make_tmap_4d(CUtensorMap* out, const void* ptr, int elem_bytes, bool is_bf16, long long rows, long long cols,
+                 long long ld, int box_cols, int box_rows, bool atom32, long long nb0, long long sb0, long long nb1,
+                 long long sb1) {
   EncodeTiledFn fn = get_encode_fn();
   if (!fn) return fail(B200_ERR_DRIVER, "cuTensorMapEncodeTiled entry point unavailable");
   if ((reinterpret_cast<uintptr_t>(ptr) & 15) != 0) return fail(B200_ERR_ARG, "TMA base pointer must be 16-byte aligned");
   if (((ld * elem_bytes) & 15) != 0) return fail(B200_ERR_ARG, "TMA row pitch (%lld B) must be a multiple of 16", ld * elem_bytes);
   if (box_cols * elem_bytes > 128 || box_rows > 256) return fail(B200_ERR_ARG, "TMA box too large");
-  cuuint64_t dims[2] = {(cuuint64_t)cols, (cuuint64_t)rows};
-  cuuint64_t strides[1] = {(cuuint64_t)(ld * elem_bytes)};
-  cuuint32_t box[2] = {(cuuint32_t)box_cols, (cuuint32_t)box_rows};
-  cuuint32_t estr[2] = {1, 1};
+  if (nb0 < 1) nb0 = 1;
+  if (nb1 < 1) nb1 = 1;
+  if (nb0 == 1 && sb0 <= 0) sb0 = ld * rows;
+  if (nb1 == 1 && sb1 <= 0) sb1 = ld * rows;
+  if (((sb0 * elem_bytes) & 15) || ((sb1 * elem_bytes) & 15)) return fail(B200_ERR_ARG, "TMA batch strides must be multiples of 16 bytes");
+  cuuint64_t dims[4] = {(cuuint64_t)cols, (cuuint64_t)rows, (cuuint64_t)nb0, (cuuint64_t)nb1};
+  cuuint64_t strides[3] = {(cuuint64_t)(ld * elem_bytes), (cuuint64_t)(sb0 * elem_bytes), (cuuint64_t)(sb1 * elem_bytes)};
+  cuuint32_t box[4] = {(cuuint32_t)box_cols, (cuuint32_t)box_rows, 1, 1};
+  cuuint32_t estr[4] = {1, 1, 1, 1};
   CUtensorMapDataType dt = elem_bytes == 4 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32
                                            : (is_bf16 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT16);
-  CUresult r = fn(out, dt, 2, const_cast<void*>(ptr), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+  CUresult r = fn(out, dt, 4, const_cast<void*>(ptr), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
                   atom32 ? CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B : CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   if (r != CUDA_SUCCESS) return fail(B200_ERR_DRIVER, "cuTensorMapEncodeTiled failed (%d) rows=%lld cols=%lld ld=%lld box=%dx%d",
                                      (int)r, rows, cols, ld, box_cols, box_rows);
@@ -385,8 +398,8 @@ static int launch_gemm(const CUtensorMap& tA, const CUtensorMap& tB, const CUten
     B200_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
     attr_set = true;
   }
-  const int tiles = args.num_m * args.num_n * args.splits;
-  const int grid = tiles < num_sms() ? tiles : num_sms();
+  const long long tiles = (long long)args.nbatch * args.num_m * args.num_n * args.splits;
+  const int grid = tiles < num_sms() ? (int)tiles : num_sms();
   kern<<<grid, kGemmThreads, smem, stream>>>(tA, tB, tD, tD2, args);
   B200_LAUNCHED("gemm_tcgen05_kernel");
   return 0;
@@ -415,7 +428,7 @@ static int dispatch_bn(int bn, bool a_mn, bool b_mn, const CUtensorMap& tA, cons
 
 // Pick the N tile: minimise (waves x tile cost); BN=64 re-reads A from smem at twice the tensor-core rate,
 // so it carries a penalty and is only chosen for very small problems.
-static int choose_bn(int M, int N, int splits) {
+static int choose_bn(int M, int N, int splits, int nbatch) {
   const int sms = num_sms();
   const int cands[4] = {256, 192, 128, 64};
   double best = 1e30;
@@ -424,7 +437,8 @@ static int choose_bn(int M, int N, int splits) {
   for (int i = 0; i < 4; ++i) {
     const int bn = cands[i];
     const int num_n = (N + bn - 1) / bn;
-    const long long tiles = (long long)num_m * num_n * splits;
+    if (bn > 64 && bn - (num_n * bn - N) <= bn / 2 && num_n == 1) continue;   // mostly-empty single tile: try narrower
+    const long long tiles = (long long)num_m * num_n * splits * nbatch;
     const long long waves = (tiles + sms - 1) / sms;
     double cost = (double)waves * (bn == 64 ? 96.0 : (double)bn) + 8.0 * waves;  // + per-tile fixed overhead
     if (cost < best - 1e-9) {
@@ -473,22 +487,26 @@ static int gemm_impl(const b200_gemm_desc* d, cudaStream_t stream) {
   int kb_per_split = (kb_total + splits - 1) / splits;
   splits = (kb_total + kb_per_split - 1) / kb_per_split;  // no empty split
 
-  const int bn = d->bn > 0 ? d->bn : choose_bn(d->M, d->N, splits);
+  const int nb0 = d->batch0 > 0 ? d->batch0 : 1;
+  const int nb1 = d->batch1 > 0 ? d->batch1 : 1;
+  const int nbatch = nb0 * nb1;
+  if (nbatch > 1 && (d->bias || d->aux || d->D2)) return fail(B200_ERR_UNSUPPORTED, "gemm: batched mode has no bias/aux/D2 epilogue");
+  const int bn = d->bn > 0 ? d->bn : choose_bn(d->M, d->N, splits, nbatch);
   if (bn != 64 && bn != 128 && bn != 192 && bn != 256) return fail(B200_ERR_ARG, "gemm: bn must be 64/128/192/256");
 
   CUtensorMap tA, tB, tD, tD2;
   int rc;
-  if (!d->a_mn) rc = make_tmap_2d(&tA, d->A, es, in_bf16, d->M, d->K, d->lda, BK, kBM);
-  else rc = make_tmap_2d(&tA, d->A, es, in_bf16, d->K, d->M, d->lda, EA, BK, es == 4);
+  if (!d->a_mn) rc = make_tmap_4d(&tA, d->A, es, in_bf16, d->M, d->K, d->lda, BK, kBM, false, nb0, d->sa0, nb1, d->sa1);
+  else rc = make_tmap_4d(&tA, d->A, es, in_bf16, d->K, d->M, d->lda, EA, BK, es == 4, nb0, d->sa0, nb1, d->sa1);
   if (rc) return rc;
-  if (!d->b_mn) rc = make_tmap_2d(&tB, d->B, es, in_bf16, d->N, d->K, d->ldb, BK, bn);
-  else rc = make_tmap_2d(&tB, d->B, es, in_bf16, d->K, d->N, d->ldb, EA, BK, es == 4);
+  if (!d->b_mn) rc = make_tmap_4d(&tB, d->B, es, in_bf16, d->N, d->K, d->ldb, BK, bn, false, nb0, d->sb0, nb1, d->sb1);
+  else rc = make_tmap_4d(&tB, d->B, es, in_bf16, d->K, d->N, d->ldb, EA, BK, es == 4, nb0, d->sb0, nb1, d->sb1);
   if (rc) return rc;
   const int CW = 128 / os;
-  rc = make_tmap_2d(&tD, d->D, os, out_bf16, d->M, d->N, d->ldd, CW, 32);
+  rc = make_tmap_4d(&tD, d->D, os, out_bf16, d->M, d->N, d->ldd, CW, 32, false, nb0, d->sd0, nb1, d->sd1);
   if (rc) return rc;
   if (d->D2) {
-    rc = make_tmap_2d(&tD2, d->D2, os, out_bf16, d->M, d->N, d->ldd, CW, 32);
+    rc = make_tmap_4d(&tD2, d->D2, os, out_bf16, d->M, d->N, d->ldd, CW, 32, false, 1, 0, 1, 0);
     if (rc) return rc;
   } else {
     tD2 = tD;
@@ -499,6 +517,8 @@ static int gemm_impl(const b200_gemm_desc* d, cudaStream_t stream) {
   a.num_m = num_m;
   a.num_n = (d->N + bn - 1) / bn;
   a.splits = splits;
+  a.nb0 = nb0;
+  a.nbatch = nbatch;
   a.kb_total = kb_total;
   a.kb_per_split = kb_per_split;
   a.bias = d->bias;

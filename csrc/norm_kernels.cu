@@ -1,0 +1,297 @@
+// norm_kernels.cu — fused  y = post_dropout( LayerNorm( pre_dropout(x + bias) + residual ) )  forward and
+// backward for sm_100a.
+//
+// Replaces the reference's unfused BertLayerNorm (mean, sub, pow, mean, add, sqrt, div, mul, add = 9
+// kernels, hetseq/bert_modeling.py:276-289) together with the dropout + residual add that precede it
+// (bert_modeling.py:387-391,423-427) and the dropout that follows the embedding LayerNorm (:306-320).
+// TF-style statistics: biased variance, eps inside the sqrt, computed in fp32 regardless of storage type.
+//
+// Dropout masks are never stored: they are regenerated from (seed, call-site stream id, element index)
+// with Philox4x32-10 in backward.  One warp owns one row; a lane holds NV float4 vectors of it.
+#include "common.h"
+#include "vec_utils.cuh"
+#include "../include/b200seq.h"
+
+namespace b200 {
+
+constexpr int kLnWarps = 8;
+constexpr int kLnThreads = kLnWarps * 32;
+constexpr int kLnBwdMaxBlocks = 296;  // 2 per SM
+
+template <typename T>
+struct LnCommon {
+  const T* x; long long ldx;
+  const T* bias;
+  const T* residual; long long ldr;
+  const T* gamma; const T* beta;
+  float eps, p_pre, p_post;
+  const unsigned long long* seed_dev;
+  unsigned long long stream_pre, stream_post;
+  int rows, cols;
+};
+
+template <typename T, int NV>
+__device__ __forceinline__ void ln_load_row(const LnCommon<T>& a, int row, int lane, const Philox& ph, uint32_t thr_pre,
+                                            float inv_keep_pre, f4 (&v)[NV], f4 (&mask)[NV]) {
+#pragma unroll
+  for (int k = 0; k < NV; ++k) {
+    const int c = (k * 32 + lane) * 4;
+    v[k] = {0.f, 0.f, 0.f, 0.f};
+    mask[k] = {1.f, 1.f, 1.f, 1.f};
+    if (c < a.cols) {
+      f4 t = load4<T>(a.x + (long long)row * a.ldx + c);
+      if (a.bias) {
+        const f4 b = load4<T>(a.bias + c);
+        t.x += b.x; t.y += b.y; t.z += b.z; t.w += b.w;
+      }
+      if (a.p_pre > 0.f) {
+        mask[k] = dropout_scale4(ph, (unsigned long long)row * a.cols + c, a.stream_pre, thr_pre, inv_keep_pre);
+        t.x *= mask[k].x; t.y *= mask[k].y; t.z *= mask[k].z; t.w *= mask[k].w;
+      }
+      if (a.residual) {
+        const f4 r = load4<T>(a.residual + (long long)row * a.ldr + c);
+        t.x += r.x; t.y += r.y; t.z += r.z; t.w += r.w;
+      }
+      v[k] = t;
+    }
+  }
+}
+
+template <typename T, int NV>
+__global__ void __launch_bounds__(kLnThreads)
+ln_fwd_kernel(const LnCommon<T> a, T* __restrict__ y, long long ldy, float* __restrict__ mean_out,
+              float* __restrict__ rstd_out) {
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const unsigned long long seed = a.seed_dev ? *a.seed_dev : 0ull;
+  const Philox ph(seed);
+  const uint32_t thr_pre = dropout_threshold(a.p_pre), thr_post = dropout_threshold(a.p_post);
+  const float ikp = a.p_pre > 0.f ? 1.f / (1.f - a.p_pre) : 1.f;
+  const float ikq = a.p_post > 0.f ? 1.f / (1.f - a.p_post) : 1.f;
+  const float inv_cols = 1.f / (float)a.cols;
+  for (int row = blockIdx.x * kLnWarps + warp; row < a.rows; row += gridDim.x * kLnWarps) {
+    f4 v[NV], mask[NV];
+    ln_load_row<T, NV>(a, row, lane, ph, thr_pre, ikp, v, mask);
+    float s = 0.f;
+#pragma unroll
+    for (int k = 0; k < NV; ++k) s += v[k].x + v[k].y + v[k].z + v[k].w;
+    const float mean = warp_sum(s) * inv_cols;
+    float q = 0.f;
+#pragma unroll
+    for (int k = 0; k < NV; ++k) {
+      const int c = (k * 32 + lane) * 4;
+      if (c < a.cols) {
+        const float d0 = v[k].x - mean, d1 = v[k].y - mean, d2 = v[k].z - mean, d3 = v[k].w - mean;
+        q += d0 * d0 + d1 * d1 + d2 * d2 + d3 * d3;
+      }
+    }
+    const float rstd = rsqrtf(warp_sum(q) * inv_cols + a.eps);
+#pragma unroll
+    for (int k = 0; k < NV; ++k) {
+      const int c = (k * 32 + lane) * 4;
+      if (c < a.cols) {
+        const f4 g = load4<T>(a.gamma + c), b = load4<T>(a.beta + c);
+        f4 o = {(v[k].x - mean) * rstd * g.x + b.x, (v[k].y - mean) * rstd * g.y + b.y,
+                (v[k].z - mean) * rstd * g.z + b.z, (v[k].w - mean) * rstd * g.w + b.w};
+        if (a.p_post > 0.f) {
+          const f4 m = dropout_scale4(ph, (unsigned long long)row * a.cols + c, a.stream_post, thr_post, ikq);
+          o.x *= m.x; o.y *= m.y; o.z *= m.z; o.w *= m.w;
+        }
+        store4<T>(y + (long long)row * ldy + c, o);
+      }
+    }
+    if (lane == 0) {
+      mean_out[row] = mean;
+      rstd_out[row] = rstd;
+    }
+  }
+}
+
+// Backward.  Per-thread register accumulators for d(gamma), d(beta), d(bias) over the rows this warp owns;
+// block partials go to scratch[block][3][cols]; ln_bwd_finalize folds them (fixed order) into the fp32
+// parameter-gradient arena with +=.
+template <typename T, int NV>
+__global__ void __launch_bounds__(kLnThreads)
+ln_bwd_kernel(const LnCommon<T> a, const T* __restrict__ dy, long long lddy, const float* __restrict__ mean_in,
+              const float* __restrict__ rstd_in, T* __restrict__ ds, long long ldds, T* __restrict__ dz, long long lddz,
+              float* __restrict__ scratch, int want_dbias) {
+  extern __shared__ float red[];  // [kLnWarps][cols]
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const unsigned long long seed = a.seed_dev ? *a.seed_dev : 0ull;
+  const Philox ph(seed);
+  const uint32_t thr_pre = dropout_threshold(a.p_pre), thr_post = dropout_threshold(a.p_post);
+  const float ikp = a.p_pre > 0.f ? 1.f / (1.f - a.p_pre) : 1.f;
+  const float ikq = a.p_post > 0.f ? 1.f / (1.f - a.p_post) : 1.f;
+  const float inv_cols = 1.f / (float)a.cols;
+  f4 acc_g[NV], acc_b[NV], acc_bias[NV];
+#pragma unroll
+  for (int k = 0; k < NV; ++k) acc_g[k] = acc_b[k] = acc_bias[k] = {0.f, 0.f, 0.f, 0.f};
+
+  for (int row = blockIdx.x * kLnWarps + warp; row < a.rows; row += gridDim.x * kLnWarps) {
+    f4 v[NV], mask[NV], g[NV];
+    ln_load_row<T, NV>(a, row, lane, ph, thr_pre, ikp, v, mask);
+    const float mean = mean_in[row], rstd = rstd_in[row];
+    float s1 = 0.f, s2 = 0.f;
+#pragma unroll
+    for (int k = 0; k < NV; ++k) {
+      const int c = (k * 32 + lane) * 4;
+      g[k] = {0.f, 0.f, 0.f, 0.f};
+      if (c < a.cols) {
+        f4 d = load4<T>(dy + (long long)row * lddy + c);
+        if (a.p_post > 0.f) {
+          const f4 m = dropout_scale4(ph, (unsigned long long)row * a.cols + c, a.stream_post, thr_post, ikq);
+          d.x *= m.x; d.y *= m.y; d.z *= m.z; d.w *= m.w;
+        }
+        const f4 gm = load4<T>(a.gamma + c);
+        // normalised input
+        v[k] = {(v[k].x - mean) * rstd, (v[k].y - mean) * rstd, (v[k].z - mean) * rstd, (v[k].w - mean) * rstd};
+        acc_g[k].x += d.x * v[k].x; acc_g[k].y += d.y * v[k].y; acc_g[k].z += d.z * v[k].z; acc_g[k].w += d.w * v[k].w;
+        acc_b[k].x += d.x; acc_b[k].y += d.y; acc_b[k].z += d.z; acc_b[k].w += d.w;
+        g[k] = {d.x * gm.x, d.y * gm.y, d.z * gm.z, d.w * gm.w};
+        s1 += g[k].x + g[k].y + g[k].z + g[k].w;
+        s2 += g[k].x * v[k].x + g[k].y * v[k].y + g[k].z * v[k].z + g[k].w * v[k].w;
+      }
+    }
+    const float c1 = warp_sum(s1) * inv_cols, c2 = warp_sum(s2) * inv_cols;
+#pragma unroll
+    for (int k = 0; k < NV; ++k) {
+      const int c = (k * 32 + lane) * 4;
+      if (c < a.cols) {
+        f4 o = {rstd * (g[k].x - c1 - v[k].x * c2), rstd * (g[k].y - c1 - v[k].y * c2),
+                rstd * (g[k].z - c1 - v[k].z * c2), rstd * (g[k].w - c1 - v[k].w * c2)};
+        if (ds) store4<T>(ds + (long long)row * ldds + c, o);
+        o.x *= mask[k].x; o.y *= mask[k].y; o.z *= mask[k].z; o.w *= mask[k].w;   // through the pre-dropout
+        if (dz) store4<T>(dz + (long long)row * lddz + c, o);
+        acc_bias[k].x += o.x; acc_bias[k].y += o.y; acc_bias[k].z += o.z; acc_bias[k].w += o.w;
+      }
+    }
+  }
+
+  // block fold: three quantities, one after the other through the same smem
+  float* out = scratch + (long long)blockIdx.x * 3 * a.cols;
+#pragma unroll 1
+  for (int qn = 0; qn < 3; ++qn) {
+    if (qn == 2 && !want_dbias) break;
+    __syncthreads();
+#pragma unroll
+    for (int k = 0; k < NV; ++k) {
+      const int c = (k * 32 + lane) * 4;
+      if (c < a.cols) {
+        const f4 t = qn == 0 ? acc_g[k] : (qn == 1 ? acc_b[k] : acc_bias[k]);
+        *reinterpret_cast<float4*>(red + warp * a.cols + c) = make_float4(t.x, t.y, t.z, t.w);
+      }
+    }
+    __syncthreads();
+    for (int c = threadIdx.x; c < a.cols; c += kLnThreads) {
+      float t = 0.f;
+#pragma unroll
+      for (int w = 0; w < kLnWarps; ++w) t += red[w * a.cols + c];
+      out[qn * a.cols + c] = t;
+    }
+  }
+}
+
+// dgamma/dbeta/dbias[c] += sum_b scratch[b][q][c]; one block = 32 columns x 8 row-lanes
+__global__ void __launch_bounds__(256)
+ln_bwd_finalize(const float* __restrict__ scratch, int nblocks, int cols, float* __restrict__ dgamma,
+                float* __restrict__ dbeta, float* __restrict__ dbias) {
+  __shared__ float red[8][33];
+  const int q = blockIdx.y;
+  float* dst = q == 0 ? dgamma : (q == 1 ? dbeta : dbias);
+  if (dst == nullptr) return;
+  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+  const int c = blockIdx.x * 32 + lane;
+  float t = 0.f;
+  if (c < cols)
+    for (int b = w; b < nblocks; b += 8) t += scratch[((long long)b * 3 + q) * cols + c];
+  red[w][lane] = t;
+  __syncthreads();
+  if (w == 0 && c < cols) {
+    float s = 0.f;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) s += red[i][lane];
+    dst[c] += s;
+  }
+}
+
+template <typename T>
+static LnCommon<T> make_common(const b200_ln_args* a) {
+  LnCommon<T> c;
+  c.x = (const T*)a->x; c.ldx = a->ldx;
+  c.bias = (const T*)a->bias;
+  c.residual = (const T*)a->residual; c.ldr = a->ldr;
+  c.gamma = (const T*)a->gamma; c.beta = (const T*)a->beta;
+  c.eps = a->eps; c.p_pre = a->p_pre; c.p_post = a->p_post;
+  c.seed_dev = a->seed_dev; c.stream_pre = a->stream_pre; c.stream_post = a->stream_post;
+  c.rows = a->rows; c.cols = a->cols;
+  return c;
+}
+
+static int check_ln(const b200_ln_args* a) {
+  if (!a || !a->x || !a->gamma || !a->beta) return fail(B200_ERR_ARG, "layernorm: null pointer");
+  if (a->cols <= 0 || a->cols > 1024 || (a->cols & 3)) return fail(B200_ERR_UNSUPPORTED, "layernorm: cols must be a multiple of 4 and <= 1024 (got %d)", a->cols);
+  if ((a->p_pre > 0.f || a->p_post > 0.f) && !a->seed_dev) return fail(B200_ERR_ARG, "layernorm: dropout needs seed_dev");
+  const int es = a->dtype == 0 ? 4 : 2;
+  if ((a->ldx * es) % (4 * es) || (a->residual && (a->ldr * es) % (4 * es))) return fail(B200_ERR_ARG, "layernorm: pitches must be multiples of 4 elements");
+  return 0;
+}
+
+template <typename T>
+static int ln_fwd_t(const b200_ln_args* a, cudaStream_t st) {
+  const LnCommon<T> c = make_common<T>(a);
+  int blocks = (a->rows + kLnWarps - 1) / kLnWarps;
+  const int cap = num_sms() * 8;
+  if (blocks > cap) blocks = cap;
+  if (a->cols <= 256) ln_fwd_kernel<T, 2><<<blocks, kLnThreads, 0, st>>>(c, (T*)a->y, a->ldy, a->mean, a->rstd);
+  else if (a->cols <= 768) ln_fwd_kernel<T, 6><<<blocks, kLnThreads, 0, st>>>(c, (T*)a->y, a->ldy, a->mean, a->rstd);
+  else ln_fwd_kernel<T, 8><<<blocks, kLnThreads, 0, st>>>(c, (T*)a->y, a->ldy, a->mean, a->rstd);
+  B200_LAUNCHED("ln_fwd_kernel");
+  return 0;
+}
+
+static int ln_bwd_blocks(int rows) {
+  int blocks = (rows + kLnWarps - 1) / kLnWarps;
+  if (blocks > kLnBwdMaxBlocks) blocks = kLnBwdMaxBlocks;
+  return blocks < 1 ? 1 : blocks;
+}
+
+template <typename T>
+static int ln_bwd_t(const b200_ln_args* a, cudaStream_t st) {
+  const LnCommon<T> c = make_common<T>(a);
+  const int blocks = ln_bwd_blocks(a->rows);
+  const size_t smem = (size_t)kLnWarps * a->cols * sizeof(float);
+  const int want_dbias = a->dbias != nullptr;
+#define LN_BWD(NV)                                                                                                   \
+  ln_bwd_kernel<T, NV><<<blocks, kLnThreads, smem, st>>>(c, (const T*)a->dy, a->lddy, a->mean, a->rstd, (T*)a->ds,    \
+                                                         a->ldds, (T*)a->dz, a->lddz, (float*)a->scratch, want_dbias)
+  if (a->cols <= 256) LN_BWD(2);
+  else if (a->cols <= 768) LN_BWD(6);
+  else LN_BWD(8);
+#undef LN_BWD
+  B200_LAUNCHED("ln_bwd_kernel");
+  dim3 grid((a->cols + 31) / 32, 3);
+  ln_bwd_finalize<<<grid, 256, 0, st>>>((const float*)a->scratch, blocks, a->cols, a->dgamma, a->dbeta, a->dbias);
+  B200_LAUNCHED("ln_bwd_finalize");
+  return 0;
+}
+
+}  // namespace b200
+
+using namespace b200;
+
+extern "C" long long b200_ln_bwd_scratch_bytes(int cols) { return (long long)kLnBwdMaxBlocks * 3 * cols * 4; }
+
+extern "C" int b200_ln_fwd(const b200_ln_args* a, void* stream) {
+  int rc = check_ln(a);
+  if (rc) return rc;
+  if (!a->y || !a->mean || !a->rstd) return fail(B200_ERR_ARG, "layernorm fwd: null output");
+  return a->dtype == 0 ? ln_fwd_t<float>(a, (cudaStream_t)stream) : ln_fwd_t<__nv_bfloat16>(a, (cudaStream_t)stream);
+}
+
+extern "C" int b200_ln_bwd(const b200_ln_args* a, void* stream) {
+  int rc = check_ln(a);
+  if (rc) return rc;
+  if (!a->dy || !a->mean || !a->rstd || !a->dgamma || !a->dbeta || !a->scratch)
+    return fail(B200_ERR_ARG, "layernorm bwd: null pointer");
+  if (a->scratch_bytes < b200_ln_bwd_scratch_bytes(a->cols)) return fail(B200_ERR_ARG, "layernorm bwd: scratch too small");
+  return a->dtype == 0 ? ln_bwd_t<float>(a, (cudaStream_t)stream) : ln_bwd_t<__nv_bfloat16>(a, (cudaStream_t)stream);
+}

@@ -91,5 +91,34 @@ def gemm(a: torch.Tensor, b: torch.Tensor, *, a_mn: bool = False, b_mn: bool = F
             raise ValueError("gemm: aux_mode without aux")
     d.act, d.aux_mode, d.accumulate, d.alpha = act, aux_mode, int(accumulate), float(alpha)
     d.bn, d.splits = bn, splits
+    d.batch0 = d.batch1 = 0
     native.check(native.cuda_lib().b200_gemm(ctypes.byref(d), _stream_ptr()), "b200_gemm")
     return out
+
+
+def bgemm(a_ptr_t: torch.Tensor, b_ptr_t: torch.Tensor, out_t: torch.Tensor, *, M: int, N: int, K: int,
+          lda: int, ldb: int, ldd: int, a_mn: bool, b_mn: bool, batch0: int, batch1: int,
+          sa=(0, 0), sb=(0, 0), sd=(0, 0), a_off: int = 0, b_off: int = 0, d_off: int = 0, alpha: float = 1.0,
+          out_fp32: bool = False, bn: int = 0) -> None:
+    """Batched GEMM over (batch1 x batch0) problems addressed by element strides — used for attention, where
+    batch0 = head and batch1 = sequence.  ``*_off`` are element offsets into the given storage tensors."""
+    es = a_ptr_t.element_size()
+    d = native.GemmDesc()
+    if a_ptr_t.dtype == torch.float32:
+        d.dtype = native.F32_TF32
+    else:
+        d.dtype = native.BF16_F32OUT if out_fp32 else native.BF16
+    d.M, d.N, d.K = M, N, K
+    d.A, d.lda, d.a_mn = a_ptr_t.data_ptr() + a_off * es, lda, int(a_mn)
+    d.B, d.ldb, d.b_mn = b_ptr_t.data_ptr() + b_off * es, ldb, int(b_mn)
+    d.D, d.ldd = out_t.data_ptr() + d_off * out_t.element_size(), ldd
+    d.D2 = d.bias = d.aux = None
+    d.ldaux = 0
+    d.act = d.aux_mode = d.accumulate = 0
+    d.alpha = float(alpha)
+    d.bn, d.splits = bn, 0
+    d.batch0, d.batch1 = batch0, batch1
+    d.sa0, d.sa1 = sa
+    d.sb0, d.sb1 = sb
+    d.sd0, d.sd1 = sd
+    native.check(native.cuda_lib().b200_gemm(ctypes.byref(d), _stream_ptr()), "b200_gemm(batched)")

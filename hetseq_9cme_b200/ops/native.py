@@ -49,6 +49,8 @@ class GemmDesc(ctypes.Structure):
         ("accumulate", c_int),
         ("alpha", c_float),
         ("bn", c_int), ("splits", c_int),
+        ("batch0", c_int), ("batch1", c_int),
+        ("sa0", c_ll), ("sa1", c_ll), ("sb0", c_ll), ("sb1", c_ll), ("sd0", c_ll), ("sd1", c_ll),
     ]
 
 

@@ -48,9 +48,141 @@ typedef struct {
   float alpha;
   int bn;                                 /* 0 = auto; else 64/128/192/256 */
   int splits;                             /* 0 = auto split-K (only when accumulate=1) */
+  /* batched mode (attention): batch index = b1 * batch0 + b0; strides in elements; 0/1 = not batched.
+   * No bias / aux / D2 epilogue in batched mode. */
+  int batch0, batch1;
+  long long sa0, sa1, sb0, sb1, sd0, sd1;
 } b200_gemm_desc;
 
 int b200_gemm(const b200_gemm_desc* d, void* stream);
+
+
+/* ------------------------------------------------------------------------------------------------
+ * Flat-arena optimizer step (all parameters / gradients / moments live in single fp32 buffers).
+ * ref: hetseq/optim.py:59-70 (multiply_grads, clip_grad_norm), :162-231 (Adam.step), :263-304
+ *      (Adadelta.step); hetseq/controller.py:338-363 (scale -> clip -> step with host syncs)
+ * ---------------------------------------------------------------------------------------------- */
+/* out[0] (=|+=) sum_i g[i]^2, deterministic.  `scratch` is caller-owned device memory of at least
+ * b200_sumsq_scratch_bytes() bytes whose last 4 bytes (arrival counter) must be zero before the first
+ * use; the kernel leaves the counter at zero again.  Launches sharing a scratch must not overlap. */
+long long b200_sumsq_scratch_bytes(void);
+int b200_sumsq_f32(const float* g, long long n, float* out, void* scratch, long long scratch_bytes,
+                   int accumulate, void* stream);
+
+typedef struct {
+  float lr, beta1, beta2, eps, weight_decay;
+  int step;                  /* 1-based update count (bias correction) */
+  float grad_scale_mult;     /* gradient scale = mult / *sample_size (or mult when sample_size is NULL) */
+  float max_norm;            /* <= 0: no clipping */
+  const float* norm_sq;      /* device: sum g^2 of the unscaled gradient; NULL: no clip, gnorm = 0 */
+  const double* sample_size; /* device: optional denominator */
+  float* stats_out;          /* device (or mapped pinned) float[3]: gnorm, applied scale, clipped flag */
+  int zero_grad;             /* 1: leave g zeroed for the next accumulation */
+} b200_adam_args;
+int b200_adam_flat(float* p, float* g, float* m, float* v, void* p_bf16 /* optional bf16 mirror */, long long n,
+                   const b200_adam_args* a, void* stream);
+
+typedef struct {
+  float lr, rho, eps, weight_decay;
+  float grad_scale_mult, max_norm;
+  const float* norm_sq;
+  const double* sample_size;
+  float* stats_out;
+  int zero_grad;
+} b200_adadelta_args;
+int b200_adadelta_flat(float* p, float* g, float* square_avg, float* acc_delta, void* p_bf16, long long n,
+                       const b200_adadelta_args* a, void* stream);
+
+/* x *= c * (c_dev ? *c_dev : 1) */
+int b200_scale_f32(float* x, long long n, float c, const float* c_dev, void* stream);
+int b200_cast_f32_to_bf16(const float* src, void* dst_bf16, long long n, void* stream);
+
+/* ------------------------------------------------------------------------------------------------
+ * Fused LayerNorm:  y = drop_post( LN( drop_pre(x + bias) + residual ) * gamma + beta )
+ * ref: hetseq/bert_modeling.py:276-289 (BertLayerNorm, eps inside sqrt), :387-391, :423-427 (dropout +
+ *      residual + LN after the attention-output / FFN-2 projections), :318-319 (embedding LN + dropout)
+ * dtype: 0 = fp32 tensors, 1 = bf16 tensors (statistics and parameter gradients are always fp32).
+ * Dropout masks are regenerated from *seed_dev + stream id + element index; nothing is stored.
+ * ---------------------------------------------------------------------------------------------- */
+typedef struct {
+  int dtype, rows, cols;
+  const void* x; long long ldx;
+  const void* bias;                         /* optional [cols] */
+  const void* residual; long long ldr;      /* optional [rows][cols] */
+  const void* gamma; const void* beta;      /* [cols] */
+  float eps, p_pre, p_post;
+  const unsigned long long* seed_dev;       /* device uint64, required when a dropout prob > 0 */
+  unsigned long long stream_pre, stream_post;
+  void* y; long long ldy;                   /* fwd out */
+  float* mean; float* rstd;                 /* fwd out / bwd in, [rows] */
+  /* backward only */
+  const void* dy; long long lddy;
+  void* ds; long long ldds;                 /* optional: grad wrt the LN input (== grad of residual) */
+  void* dz; long long lddz;                 /* optional: grad wrt x (ds through the pre-dropout mask) */
+  float* dgamma; float* dbeta; float* dbias;/* fp32 [cols], accumulated with +=; dbias optional */
+  void* scratch; long long scratch_bytes;   /* >= b200_ln_bwd_scratch_bytes(cols); contents need no init */
+} b200_ln_args;
+long long b200_ln_bwd_scratch_bytes(int cols);
+int b200_ln_fwd(const b200_ln_args* a, void* stream);
+int b200_ln_bwd(const b200_ln_args* a, void* stream);
+
+/* ------------------------------------------------------------------------------------------------
+ * Embeddings, masked-row compaction, cross-entropy, tiny-N heads, column sums.
+ * dtype: 0 = fp32 tensors, 1 = bf16 tensors.  Parameter gradients are always fp32 and accumulated (+=).
+ * ref: hetseq/bert_modeling.py:306-320 (BertEmbeddings), :899-905 (MLM + NSP CrossEntropyLoss),
+ *      :576-581 (heads), :1221-1245 (token-classification head + masked CE)
+ * ---------------------------------------------------------------------------------------------- */
+/* out[r] = W[ids[r]] + P[r % L] + TT[tts[r]] */
+int b200_embed_sum(int dtype, const long long* ids, const long long* tts, const void* W, const void* P, const void* TT,
+                   void* out, int rows, int L, int H, int vocab, int ntypes, void* stream);
+/* gW[ids[r]] += ds[r]; gP[r % L] += ds[r]; gT[tts[r]] += ds[r]   (fp32 vector reductions at L2) */
+int b200_embed_scatter(int dtype, const long long* ids, const long long* tts, const void* ds, float* gW, float* gP,
+                       float* gT, int rows, int L, int H, int vocab, int ntypes, void* stream);
+/* order-preserving compaction of rows with labels != ignore (and mask != 0): idx_out/label_out have `cap`
+ * entries (tail = -1 / ignore); count_out = {min(n,cap), n} */
+int b200_compact_rows(const long long* labels, const long long* mask, int rows, int ignore, int cap, int* idx_out,
+                      long long* label_out, int* count_out, void* stream);
+int b200_gather_rows(int dtype, const void* x, long long ldx, const int* idx, int n, int H, void* out, void* stream);
+int b200_scatter_rows(int dtype, const void* dy, const int* idx, int n, int H, void* dx, long long lddx, int accumulate,
+                      void* stream);
+/* wide softmax cross-entropy: per-row logsumexp + loss; backward overwrites logits with d(logits) */
+int b200_ce_fwd(int dtype, const void* logits, long long ld, const long long* labels, int rows, int V, int ignore,
+                float* lse, float* row_loss, void* stream);
+int b200_ce_bwd(int dtype, void* logits, long long ld, const long long* labels, int rows, int V, int ignore,
+                const float* lse, const float* gout, const float* inv_count, void* stream);
+/* loss = sum(row_loss)/max(#valid,1); inv_count = 1/max(#valid,1) */
+int b200_ce_finalize(const float* row_loss, const long long* labels, int rows, int ignore, float* loss, float* inv_count,
+                     float* count_out, void* stream);
+/* tiny heads (1 <= N <= 32): fp32 logits */
+int b200_head_fwd(int dtype, const void* x, long long ldx, const void* w, const void* b, int rows, int K, int N, float* out,
+                  void* stream);
+int b200_head_ce(const float* logits, const long long* labels, const long long* active, int rows, int N, int ignore,
+                 float* row_loss, long long* eff_labels, void* stream);
+int b200_head_ce_bwd(const float* logits, const long long* eff_labels, int rows, int N, int ignore, const float* gout,
+                     const float* inv_count, float* dlogits, void* stream);
+int b200_head_bwd(int dtype, const float* dl, const void* x, long long ldx, const void* w, int rows, int K, int N, void* dx,
+                  long long lddx, int accumulate_dx, float* dw, float* db, void* stream);
+/* out = dy * act'(aux); mode 1: gelu' at pre-activation aux, mode 2: tanh' = 1 - aux^2 at output aux */
+int b200_act_bwd(int dtype, const void* dy, const void* aux, void* out, long long n, int mode, void* stream);
+/* y = x * keep_mask/(1-p) (n % 4 == 0); the same call on a gradient is the backward */
+int b200_dropout(int dtype, const void* x, void* y, long long n, float p, const unsigned long long* seed_dev,
+                 unsigned long long stream_id, void* stream);
+/* out[c] += sum_r x[r][c]; scratch >= b200_colsum_scratch_bytes(rows, cols), no init needed */
+long long b200_colsum_scratch_bytes(int rows, int cols);
+int b200_colsum(int dtype, const void* x, long long ldx, int rows, int cols, float* out, void* scratch,
+                long long scratch_bytes, void* stream);
+
+/* ------------------------------------------------------------------------------------------------
+ * Attention softmax over scores S[B][heads][L][Lp] produced by the batched GEMM (already scaled):
+ * P = softmax(S + (1-mask)*-10000) written over S; Pdrop = dropout(P) (only when p_drop > 0).
+ * Backward: dP <- P * (dPe - rowsum(P*dPe)), dPe = dP through the regenerated dropout mask.
+ * ref: hetseq/bert_modeling.py:361-371 (scores/sqrt(d) + mask, Softmax, Dropout), :817-825 (mask)
+ * ---------------------------------------------------------------------------------------------- */
+int b200_softmax_fwd(int dtype, void* S, void* Pdrop, const long long* attn_mask /* [B][L] 0/1, optional */, int B,
+                     int heads, int L, int Lp, float p_drop, const unsigned long long* seed_dev,
+                     unsigned long long stream_id, void* stream);
+int b200_softmax_bwd(int dtype, const void* P, void* dP, int B, int heads, int L, int Lp, float p_drop,
+                     const unsigned long long* seed_dev, unsigned long long stream_id, void* stream);
 
 #ifdef __cplusplus
 }

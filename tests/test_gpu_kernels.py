@@ -1,0 +1,301 @@
+"""Numerics of every hand-written kernel against a plain PyTorch fp32/fp64 restatement of the same op."""
+import math
+
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+
+def _rel(a, b):
+    return (a.double() - b.double()).abs().max().item() / (b.double().abs().max().item() + 1e-12)
+
+
+@pytest.fixture(scope="module")
+def K():
+    from hetseq_9cme_b200.ops import kernels
+    return kernels
+
+
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+@pytest.mark.parametrize("majors", [(False, False), (False, True), (True, True), (True, False)])
+def test_gemm_layouts(dtype, majors):
+    from hetseq_9cme_b200.ops.gemm import gemm
+    a_mn, b_mn = majors
+    torch.manual_seed(0)
+    M, N, K_ = 384, 320, 200 if dtype == torch.float32 else 208
+    a = torch.randn((K_, M) if a_mn else (M, K_), device="cuda").to(dtype)
+    b = torch.randn((K_, N) if b_mn else (N, K_), device="cuda").to(dtype)
+    out = gemm(a, b, a_mn=a_mn, b_mn=b_mn)
+    A = a.double().t() if a_mn else a.double()
+    Bm = b.double().t() if b_mn else b.double()
+    ref = A @ Bm.t()
+    assert _rel(out, ref) < (5e-3 if dtype == torch.float32 else 2e-2)
+
+
+def test_gemm_epilogues_and_accumulate():
+    from hetseq_9cme_b200.ops.gemm import gemm
+    from hetseq_9cme_b200.ops import native as nat
+    torch.manual_seed(1)
+    M, N, Kd = 256, 512, 256
+    a = torch.randn(M, Kd, device="cuda")
+    w = torch.randn(N, Kd, device="cuda") * 0.1
+    bias = torch.randn(N, device="cuda")
+    aux = torch.randn(M, N, device="cuda")
+    base = a.double() @ w.double().t()
+    pre = torch.empty(M, N, device="cuda")
+    got = gemm(a, w, bias=bias, act=nat.ACT_GELU, preact_out=pre)
+    assert _rel(pre, base + bias.double()) < 5e-3
+    assert _rel(got, torch.nn.functional.gelu(base + bias.double())) < 5e-3
+    assert _rel(gemm(a, w, bias=bias, aux=aux, aux_mode=nat.AUX_ADD), base + bias.double() + aux.double()) < 5e-3
+    x = aux.double().requires_grad_(True)
+    torch.nn.functional.gelu(x).sum().backward()
+    assert _rel(gemm(a, w, aux=aux, aux_mode=nat.AUX_MUL_DGELU), base * x.grad) < 5e-3
+    acc = torch.ones(M, N, device="cuda")
+    gemm(a, w, out=acc, accumulate=True, splits=2)
+    assert _rel(acc, base + 1.0) < 5e-3
+
+
+def test_batched_gemm_attention_shapes():
+    from hetseq_9cme_b200.ops.gemm import bgemm
+    torch.manual_seed(2)
+    B, h, L, dh = 3, 4, 80, 64
+    H = h * dh
+    Lp = (L + 7) // 8 * 8
+    qkv = torch.randn(B * L, 3 * H, device="cuda")
+    S = torch.zeros(B, h, L, Lp, device="cuda")
+    bgemm(qkv, qkv, S, M=L, N=L, K=dh, lda=3 * H, ldb=3 * H, ldd=Lp, a_mn=False, b_mn=False, batch0=h, batch1=B,
+          sa=(dh, L * 3 * H), sb=(dh, L * 3 * H), sd=(L * Lp, h * L * Lp), b_off=H, alpha=0.125)
+    q = qkv.view(B, L, 3, h, dh)[:, :, 0].permute(0, 2, 1, 3).double()
+    k = qkv.view(B, L, 3, h, dh)[:, :, 1].permute(0, 2, 1, 3).double()
+    v = qkv.view(B, L, 3, h, dh)[:, :, 2].permute(0, 2, 1, 3).double()
+    ref = (q @ k.transpose(-1, -2)) * 0.125
+    assert _rel(S[..., :L], ref) < 5e-3
+    P = torch.softmax(ref, -1).float()
+    Pp = torch.zeros(B, h, L, Lp, device="cuda")
+    Pp[..., :L] = P
+    ctx = torch.empty(B * L, H, device="cuda")
+    bgemm(Pp, qkv, ctx, M=L, N=dh, K=L, lda=Lp, ldb=3 * H, ldd=H, a_mn=False, b_mn=True, batch0=h, batch1=B,
+          sa=(L * Lp, h * L * Lp), sb=(dh, L * 3 * H), sd=(dh, L * H), b_off=2 * H)
+    refc = (P.double() @ v).permute(0, 2, 1, 3).reshape(B * L, H)
+    assert _rel(ctx, refc) < 5e-3
+    # MN-major A (transposed probabilities) as used by dV
+    dctx = torch.randn(B * L, H, device="cuda")
+    dqkv = torch.zeros(B * L, 3 * H, device="cuda")
+    bgemm(Pp, dctx, dqkv, M=L, N=dh, K=L, lda=Lp, ldb=H, ldd=3 * H, a_mn=True, b_mn=True, batch0=h, batch1=B,
+          sa=(L * Lp, h * L * Lp), sb=(dh, L * H), sd=(dh, L * 3 * H), d_off=2 * H)
+    dc = dctx.view(B, L, h, dh).permute(0, 2, 1, 3).double()
+    refdv = (P.double().transpose(-1, -2) @ dc).permute(0, 2, 1, 3).reshape(B * L, H)
+    assert _rel(dqkv[:, 2 * H:], refdv) < 5e-3
+
+
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+@pytest.mark.parametrize("cols", [128, 768, 1024])
+def test_layernorm_fwd_bwd(K, dtype, cols):
+    torch.manual_seed(3)
+    rows = 515
+    x = torch.randn(rows, cols, device="cuda").to(dtype)
+    res = torch.randn(rows, cols, device="cuda").to(dtype)
+    bias = torch.randn(cols, device="cuda").to(dtype)
+    gamma = (torch.rand(cols, device="cuda") + 0.5).to(dtype)
+    beta = torch.randn(cols, device="cuda").to(dtype)
+    y, mean, rstd = K.ln_fwd(x, gamma, beta, bias=bias, residual=res, eps=1e-12)
+    xr = (x.double() + bias.double() + res.double()).requires_grad_(True)
+    gr, br = gamma.double().requires_grad_(True), beta.double().requires_grad_(True)
+    mu = xr.mean(-1, keepdim=True)
+    var = (xr - mu).pow(2).mean(-1, keepdim=True)
+    yr = (xr - mu) / torch.sqrt(var + 1e-12) * gr + br
+    tol = 1e-4 if dtype == torch.float32 else 2e-2
+    assert _rel(y, yr) < tol
+    dy = torch.randn(rows, cols, device="cuda").to(dtype)
+    yr.backward(dy.double())
+    dg = torch.zeros(cols, device="cuda")
+    db = torch.zeros(cols, device="cuda")
+    dbias = torch.zeros(cols, device="cuda")
+    ds, dz = K.ln_bwd(dy, x, gamma, beta, mean, rstd, dg, db, bias=bias, dbias=dbias, residual=res, eps=1e-12)
+    assert dz is None
+    assert _rel(ds, xr.grad) < tol
+    assert _rel(dg, gr.grad) < tol
+    assert _rel(db, br.grad) < tol
+    assert _rel(dbias, xr.grad.sum(0)) < tol
+
+
+def test_layernorm_dropout_is_consistent(K):
+    """Forward and backward must regenerate the same mask; keep-rate must match p."""
+    torch.manual_seed(4)
+    rows, cols, p = 2048, 768, 0.1
+    ws = K.Workspace.get("cuda")
+    ws.set_seed(1234)
+    x = torch.randn(rows, cols, device="cuda")
+    gamma, beta = torch.ones(cols, device="cuda"), torch.zeros(cols, device="cuda")
+    # post-dropout: zeros in y mark dropped elements
+    y, mean, rstd = K.ln_fwd(x, gamma, beta, p_post=p, seed=ws.seed, stream_post=5)
+    dropped = (y == 0)
+    rate = dropped.float().mean().item()
+    assert abs(rate - p) < 0.01
+    dy = torch.ones_like(x)
+    dg, db = torch.zeros(cols, device="cuda"), torch.zeros(cols, device="cuda")
+    K.ln_bwd(dy, x, gamma, beta, mean, rstd, dg, db, p_post=p, seed=ws.seed, stream_post=5)
+    # d(beta) = sum over rows of the masked dy = kept count * 1/(1-p)
+    kept = (~dropped).float().sum(0) / (1 - p)
+    assert _rel(db, kept) < 1e-5
+    y2, _, _ = K.ln_fwd(x, gamma, beta, p_post=p, seed=ws.seed, stream_post=6)
+    assert (y2 == 0).ne(dropped).any()          # a different stream id gives a different mask
+
+
+def test_softmax_fwd_bwd(K):
+    torch.manual_seed(5)
+    B, h, L = 2, 3, 100
+    Lp = 104
+    S = torch.randn(B, h, L, Lp, device="cuda")
+    mask = torch.ones(B, L, dtype=torch.int64, device="cuda")
+    mask[1, 70:] = 0
+    ref_in = S[..., :L].double() + ((1 - mask.double()) * -10000.0)[:, None, None, :]
+    ref_in.requires_grad_(True)
+    Pr = torch.softmax(ref_in, -1)
+    Sg = S.clone()
+    K.softmax_fwd_(Sg, mask, B, h, L, Lp)
+    assert _rel(Sg[..., :L], Pr) < 1e-5
+    assert Sg[..., L:].abs().max().item() == 0
+    dP = torch.randn(B, h, L, Lp, device="cuda")
+    dP[..., L:] = 0
+    Pr.backward(dP[..., :L].double())
+    K.softmax_bwd_(Sg, dP, B, h, L, Lp)
+    assert _rel(dP[..., :L], ref_in.grad) < 1e-4
+
+
+def test_cross_entropy_wide(K):
+    torch.manual_seed(6)
+    rows, V = 96, 30522
+    ld = (V + 3) // 4 * 4
+    logits = (torch.randn(rows, ld, device="cuda") * 3)[:, :V]        # padded pitch, as produced by gemm()
+    labels = torch.randint(0, V, (rows,), device="cuda")
+    labels[::5] = -1
+    ref_l = logits.double().clone().requires_grad_(True)
+    ref = torch.nn.functional.cross_entropy(ref_l, labels, ignore_index=-1)
+    lse, row_loss = K.ce_fwd(logits, labels, ignore=-1)
+    loss, inv, cnt = K.ce_finalize(row_loss, labels, ignore=-1)
+    assert abs(loss.item() - ref.item()) < 1e-4
+    ref.backward()
+    g = torch.full((1,), 1.0, device="cuda")
+    K.ce_bwd_(logits, labels, lse, gout=g, inv_count=inv, ignore=-1)
+    assert _rel(logits, ref_l.grad) < 1e-4
+
+
+def test_embedding_and_scatter(K):
+    torch.manual_seed(7)
+    B, L, H, V = 4, 32, 128, 1000
+    W, P, T = torch.randn(V, H, device="cuda"), torch.randn(64, H, device="cuda"), torch.randn(2, H, device="cuda")
+    ids = torch.randint(0, V, (B, L), device="cuda")
+    tts = torch.randint(0, 2, (B, L), device="cuda")
+    out = K.embed_sum(ids.view(-1), tts.view(-1), W, P, T, L)
+    pos = torch.arange(L, device="cuda").repeat(B)
+    ref = W[ids.view(-1)] + P[pos] + T[tts.view(-1)]
+    assert _rel(out, ref) < 1e-6
+    ds = torch.randn(B * L, H, device="cuda")
+    gW, gP, gT = torch.zeros_like(W), torch.zeros_like(P), torch.zeros_like(T)
+    K.embed_scatter(ids.view(-1), tts.view(-1), ds, gW, gP, gT, L)
+    rW = torch.zeros_like(W).index_add_(0, ids.view(-1), ds)
+    rP = torch.zeros_like(P).index_add_(0, pos, ds)
+    rT = torch.zeros_like(T).index_add_(0, tts.view(-1), ds)
+    assert _rel(gW, rW) < 1e-5 and _rel(gP, rP) < 1e-5 and _rel(gT, rT) < 1e-5
+
+
+def test_compact_gather_scatter(K):
+    torch.manual_seed(8)
+    rows, H = 3000, 64
+    labels = torch.full((rows,), -1, dtype=torch.int64, device="cuda")
+    sel = torch.randperm(rows, device="cuda")[:400].sort().values
+    labels[sel] = torch.randint(0, 100, (400,), device="cuda")
+    idx, lab, cnt = K.compact_rows(labels, 512, ignore=-1)
+    assert cnt.tolist() == [400, 400]
+    assert torch.equal(idx[:400].long(), sel) and (idx[400:] == -1).all()
+    assert torch.equal(lab[:400], labels[sel])
+    x = torch.randn(rows, H, device="cuda")
+    g = K.gather_rows(x, idx)
+    assert torch.equal(g[:400], x[sel]) and g[400:].abs().max().item() == 0
+    dx = torch.zeros(rows, H, device="cuda")
+    K.scatter_rows(g, idx, dx)
+    assert torch.equal(dx[sel], x[sel])
+
+
+def test_small_heads(K):
+    torch.manual_seed(9)
+    rows, Kd, N = 700, 256, 9
+    x = torch.randn(rows, Kd, device="cuda")
+    w = torch.randn(N, Kd, device="cuda") * 0.1
+    b = torch.randn(N, device="cuda")
+    labels = torch.randint(0, N, (rows,), device="cuda")
+    labels[::7] = -100
+    active = torch.ones(rows, dtype=torch.int64, device="cuda")
+    active[::3] = 0
+    xr, wr, br = x.double().requires_grad_(True), w.double().requires_grad_(True), b.double().requires_grad_(True)
+    lr_ = xr @ wr.t() + br
+    eff = torch.where(active == 1, labels, torch.full_like(labels, -100))
+    ref = torch.nn.functional.cross_entropy(lr_, eff, ignore_index=-100)
+    ref.backward()
+    logits = K.head_fwd(x, w, b)
+    assert _rel(logits, lr_) < 1e-5
+    rl, effk = K.head_ce(logits, labels, active, ignore=-100)
+    loss, inv, _ = K.ce_finalize(rl, effk, ignore=-100)
+    assert abs(loss.item() - ref.item()) < 1e-5
+    dl = K.head_ce_bwd(logits, effk, gout=None, inv_count=inv, ignore=-100)
+    dx = torch.empty_like(x)
+    dw, db = torch.zeros_like(w), torch.zeros_like(b)
+    K.head_bwd(dl, x, w, dx=dx, dw=dw, db=db)
+    assert _rel(dx, xr.grad) < 1e-4 and _rel(dw, wr.grad) < 1e-4 and _rel(db, br.grad) < 1e-4
+
+
+def test_colsum_actbwd_dropout(K):
+    torch.manual_seed(10)
+    x = torch.randn(4096, 768, device="cuda")
+    out = torch.ones(768, device="cuda")
+    K.colsum_(x, out)
+    assert _rel(out, x.double().sum(0) + 1) < 1e-5
+    u = torch.randn(512, 768, device="cuda")
+    ur = u.double().requires_grad_(True)
+    torch.nn.functional.gelu(ur).sum().backward()
+    dy = torch.randn_like(u)
+    assert _rel(K.act_bwd(dy, u, 1), dy.double() * ur.grad) < 1e-5
+    ws = K.Workspace.get("cuda")
+    ws.set_seed(77)
+    y = K.dropout(x, 0.25, ws.seed, 3)
+    keep = (y != 0)
+    assert abs(keep.float().mean().item() - 0.75) < 0.01
+    assert _rel(y[keep], x[keep] / 0.75) < 1e-6
+    assert torch.equal(K.dropout(x, 0.25, ws.seed, 3), y)
+
+
+def test_sumsq_and_adam_match_reference_math(K):
+    torch.manual_seed(11)
+    n = 1_000_003
+    npad = (n + 63) // 64 * 64
+    p = torch.randn(npad, device="cuda")
+    g = torch.randn(npad, device="cuda") * 0.01
+    m = torch.zeros(npad, device="cuda")
+    v = torch.zeros(npad, device="cuda")
+    ws = K.Workspace.get("cuda")
+    K.sumsq(g, ws.norm_sq)
+    assert abs(ws.norm_sq.item() - g.double().pow(2).sum().item()) / g.double().pow(2).sum().item() < 1e-5
+    # reference Adam math (hetseq/optim.py:206-229) in float64
+    lr, b1, b2, eps, wd = 1e-3, 0.9, 0.999, 1e-8, 0.01
+    mult, ss, max_norm = 8.0, 128.0, 0.05
+    pr, gr, mr, vr = p.double(), g.double(), m.double(), v.double()
+    c = mult / ss
+    gnorm = gr.norm().item() * c
+    coef = max_norm / (gnorm + 1e-6) if gnorm > max_norm else 1.0
+    for step in (1, 2):
+        gs = gr * c * coef
+        mr = b1 * mr + (1 - b1) * gs
+        vr = b2 * vr + (1 - b2) * gs * gs
+        denom = vr.sqrt() + eps
+        step_size = lr * math.sqrt(1 - b2 ** step) / (1 - b1 ** step)
+        pr = pr * (1 - wd * lr) - step_size * mr / denom
+    sample = torch.tensor([ss], dtype=torch.float64, device="cuda")
+    stats = torch.zeros(4, device="cuda")
+    for step in (1, 2):
+        K.sumsq(g, ws.norm_sq)
+        K.adam_flat(p, g, m, v, npad, lr=lr, beta1=b1, beta2=b2, eps=eps, weight_decay=wd, step=step, grad_scale_mult=mult,
+                    max_norm=max_norm, norm_sq=ws.norm_sq, sample_size=sample, stats_out=stats, zero_grad=False)
+    assert _rel(p, pr) < 1e-5
+    assert abs(stats[0].item() - gnorm) / gnorm < 1e-4 and stats[2].item() == 1.0

@@ -1,0 +1,262 @@
+#!/usr/bin/env python3
+"""Headline benchmark: BERT-base phase-1 pre-training (seq 128, per-GPU batch 32) sequences/second.
+
+    python bench.py --gpus N --steps K --warmup W            # ours
+    python bench.py --impl reference --gpus N ...            # the unmodified reference from baseline/_ref
+
+For N > 1 the driver launches it under ``torch.distributed.run`` (one rank per GPU, NCCL rendezvous from the
+environment).  Rank 0 prints ONE JSON line.  Two numbers are measured on the same model / data / step function:
+
+* ``value``      — device-timed (CUDA events, max over ranks) throughput of K full training steps (forward,
+                    backward, gradient reduction, clip, Adam) with the step's inputs already resident on the
+                    device; working set per step (440 MB weights + activations) is far larger than the 126 MB L2;
+* ``e2e.value``  — the same K steps driven through the public API the CLI uses (task batch iterator ->
+                    ``Controller.train_step``): every step copies its inputs host->device from pinned memory and
+                    the step's loss / grad-norm come back device->host; wall-clock bracketed by synchronize.
+
+Data is synthetic (random token ids in the NVIDIA shard schema, written to a temp dir in this framework's
+``.b2s`` shard format) and weights are random-initialised: there is no network on the box.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import shutil
+import subprocess
+import sys
+import tempfile
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+PUBLISHED_SEQ_PER_SEC_PER_GPU = 12.3   # 49.2 seq/s on 4 GPUs (README.md:65 of the reference)
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--precision", default="tf32", choices=["tf32", "bf16"])
+    ap.add_argument("--batch", type=int, default=32, help="per-GPU batch (reference scripts use 32)")
+    ap.add_argument("--seq-len", type=int, default=128)
+    ap.add_argument("--model", default="bert-base", choices=["bert-base", "bert-large", "bert-tiny"])
+    ap.add_argument("--comm", default="auto")
+    ap.add_argument("--no-e2e", action="store_true")
+    return ap.parse_args()
+
+
+MODELS = {
+    "bert-base": dict(hidden_size=768, num_hidden_layers=12, num_attention_heads=12, intermediate_size=3072),
+    "bert-large": dict(hidden_size=1024, num_hidden_layers=24, num_attention_heads=16, intermediate_size=4096),
+    "bert-tiny": dict(hidden_size=128, num_hidden_layers=2, num_attention_heads=2, intermediate_size=512),
+}
+
+
+class ClockSampler:
+    """Samples SM clock / throttle reasons with nvidia-smi every 200 ms while the timed region runs."""
+
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index: int):
+        self.gpu = gpu_index
+        self.proc = None
+        self.lines = []
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.gpu), "--query-gpu=" + self.Q,
+                                          "--format=csv,noheader,nounits", "-lms", "200"], stdout=subprocess.PIPE,
+                                         stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.lines.append(line.strip())
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=2)
+        except Exception:
+            self.proc.kill()
+        sm, mx, reasons = [], [], set()
+        for ln in self.lines:
+            f = [x.strip() for x in ln.split(",")]
+            if len(f) < 9:
+                continue
+            try:
+                sm.append(float(f[1])); mx.append(float(f[2]))
+            except ValueError:
+                continue
+            for name, val in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), f[5:9]):
+                if val.lower().startswith("active"):
+                    reasons.add(name)
+        sm.sort()
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def _dist_env():
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    return rank, local, world
+
+
+def make_args(a, data_dir, cfg_path, vocab_path, rank, local, world):
+    from hetseq_9cme_b200 import options
+    argv = ["--task", "bert", "--optimizer", "adam", "--data", data_dir, "--dict", vocab_path, "--config_file", cfg_path,
+            "--max-sentences", str(a.batch), "--max-epoch", "1000", "--lr", "1e-4", "--warmup-updates", "100",
+            "--total-num-update", "100000", "--weight-decay", "0.01", "--clip-norm", "25", "--fast-stat-sync",
+            "--valid-subset", "test", "--num-workers", "2", "--save-dir", os.path.join(data_dir, "ckpt"), "--no-save",
+            "--log-format", "none", "--distributed-world-size", str(world), "--precision", a.precision, "--comm", a.comm,
+            "--max-predictions-per-seq", "20" if a.seq_len <= 128 else "80", "--disable-validation"]
+    args = options.parse_training_args(argv)
+    args.distributed_rank = rank
+    args.device_id = local
+    return args
+
+
+def run_ours(a):
+    import torch
+    import torch.distributed as dist
+    rank, local, world = _dist_env()
+    if world != a.gpus and world > 1:
+        a.gpus = world
+    torch.cuda.set_device(local)
+    if world > 1 and not dist.is_initialized():
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    from hetseq_9cme_b200 import tasks
+    from hetseq_9cme_b200.controller import Controller
+    from hetseq_9cme_b200.data import synthetic
+    from hetseq_9cme_b200.ops import native
+
+    tmp = tempfile.mkdtemp(prefix="b200bench_r%d_" % rank)
+    try:
+        nsteps_needed = a.steps + a.warmup + 4
+        per_rank = nsteps_needed * a.batch
+        max_pred = 20 if a.seq_len <= 128 else 80
+        synthetic.make_bert_shards(tmp, n_train_files=2, samples_per_file=(per_rank * world + 1) // 2 + a.batch,
+                                   seq_len=a.seq_len, max_pred=max_pred, fmt="b2s", seed=1234, test_samples=a.batch)
+        cfg_path = synthetic.write_bert_config(os.path.join(tmp, "bert_config.json"), **MODELS[a.model])
+        vocab_path = synthetic.write_vocab(os.path.join(tmp, "vocab.txt"))
+        args = make_args(a, tmp, cfg_path, vocab_path, rank, local, world)
+        torch.manual_seed(args.seed)
+        task = tasks.LanguageModelingTask.setup_task(args)
+        task.load_dataset("test")
+        model = task.build_model(args)
+        controller = Controller(args, task, model)
+        epoch_itr = controller.get_train_iterator(epoch=0, load_dataset=True)
+        controller.lr_step(epoch_itr.epoch)
+        itr = epoch_itr.next_epoch_itr(shuffle=True)
+
+        def sync_all():
+            torch.cuda.synchronize()
+            if world > 1:
+                dist.barrier()
+                torch.cuda.synchronize()
+
+        # ---- warm-up through the public path ------------------------------------------------------------
+        staged = []
+        for _ in range(a.warmup):
+            sample = next(itr)
+            controller.train_step([sample])
+            staged.append([t.cuda(non_blocking=True) for t in sample])
+        controller.flush_stats()
+        sync_all()
+
+        # ---- device-timed region: inputs resident ---------------------------------------------------------
+        while len(staged) < 4:
+            staged.append([t.cuda() for t in next(itr)])
+        sampler = ClockSampler(local)
+        sampler.start()
+        native.reset_launch_count()
+        sync_all()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for s in range(a.steps):
+            controller.train_step([staged[s % len(staged)]])
+        e1.record()
+        sync_all()
+        dev_ms = e0.elapsed_time(e1)
+        launches = native.launch_count()
+        controller.flush_stats()
+        loss_dev = controller.get_meter("train_loss").avg
+
+        # ---- end-to-end region: pinned host batches -> H2D -> step -> D2H stats, every step ------------------
+        e2e = None
+        if not a.no_e2e:
+            sync_all()
+            h2d = d2h = 0
+            t0 = time.perf_counter()
+            for s in range(a.steps):
+                sample = next(itr)
+                h2d += sum(t.numel() * t.element_size() for t in sample)
+                out = controller.train_step([sample])
+                d2h += 8 * 8
+            controller.flush_stats()           # host has read every step's loss / gnorm
+            sync_all()
+            e2e_ms = (time.perf_counter() - t0) * 1e3
+        clocks = sampler.stop()
+
+        t = torch.tensor([dev_ms, e2e_ms if not a.no_e2e else 0.0], device="cuda", dtype=torch.float64)
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        dev_ms, e2e_ms = t.tolist()
+        gb = a.batch * world
+        value = gb * a.steps / (dev_ms / 1e3)
+        out = {
+            "metric": "BERT-base phase-1 pre-training throughput (seq 128)" if a.model == "bert-base" else a.model + " throughput",
+            "value": round(value, 2), "unit": "sequences/s", "n_gpus": world, "steps": a.steps, "warmup": a.warmup,
+            "ms_per_step": round(dev_ms / a.steps, 4), "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": round(value / (PUBLISHED_SEQ_PER_SEC_PER_GPU * world), 2), "dtype": a.precision, "data": "synthetic",
+            "impl": "ours",
+            "config": {"model": a.model, "global_batch": gb, "per_gpu_batch": a.batch, "seq_len": a.seq_len,
+                       "parallelism": "dp%d" % world, "optimizer": "adam (fused, fp32 master)", "dropout": 0.1,
+                       "max_predictions_per_seq": max_pred, "l2_policy": "per-step working set (>= 440 MB) exceeds the 126 MB L2",
+                       "timing": "CUDA events on the training stream, max over ranks", "comm": type(controller.reducer).__name__,
+                       "baseline_ref": "12.3 seq/s/GPU published (reference README.md:65, Pascal-era GPUs)"},
+            "clocks": clocks, "gpu_launches": int(launches), "final_loss": round(float(loss_dev), 4),
+        }
+        if not a.no_e2e:
+            out["e2e"] = {"value": round(gb * a.steps / (e2e_ms / 1e3), 2), "unit": "sequences/s",
+                          "ms_per_step": round(e2e_ms / a.steps, 4), "h2d_bytes_per_step": int(h2d / a.steps),
+                          "d2h_bytes_per_step": int(d2h / a.steps)}
+        if rank == 0:
+            print(json.dumps(out), flush=True)
+        if world > 1:
+            dist.barrier()
+    finally:
+        shutil.rmtree(tmp, ignore_errors=True)
+
+
+def main():
+    a = parse()
+    if a.impl == "reference":
+        from baseline.run_reference import run_reference
+        return run_reference(a)
+    try:
+        import torch
+        if not torch.cuda.is_available():
+            print(json.dumps({"impl": "ours", "unavailable": "no CUDA device visible"}))
+            return 0
+    except Exception as e:  # pragma: no cover
+        print(json.dumps({"impl": "ours", "unavailable": str(e)}))
+        return 0
+    run_ours(a)
+    return 0
+
+
+if __name__ == "__main__":
+    sys.exit(main())

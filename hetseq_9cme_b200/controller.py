@@ -1,0 +1,458 @@
+"""The trainer ("Controller").
+
+Public surface of hetseq/controller.py:22-440 — ``train_step``, ``save_checkpoint`` / ``load_checkpoint``,
+``get_train_iterator``, ``lr_step`` / ``lr_step_update`` / ``get_lr``, ``get_model`` / ``get_meter`` /
+``get_num_updates`` / ``set_num_updates`` / ``zero_grad``, lazy ``model`` / ``optimizer`` / ``lr_scheduler`` — plus a
+working ``valid_step`` (the reference stubs validation out, hetseq/train.py:99-100).
+
+What is different underneath:
+
+* no ``DistributedDataParallel``: parameters, gradients and optimizer moments live in flat arenas
+  (``parallel/arena.py``); a reducer (``parallel/reducer.py``) sums gradient buckets across ranks while backward
+  is still running;
+* gradient scale ``W / sample_size`` (after DDP's ``1/W`` average — i.e. ``1 / sample_size`` on the summed
+  gradient), global-norm clip, the optimizer update and ``zero_grad`` are ONE kernel driven by device scalars;
+* the step never waits for the GPU: loss / grad-norm travel to a pinned mailbox asynchronously and feed the
+  meters one step later (``flush_stats`` forces them, e.g. before a log line at the end of an epoch);
+* inputs go to the device with non-blocking copies from pinned memory.
+
+Reference quirks that are kept on purpose: ``sample_size`` semantics come from the task (sequence
+length for BERT, 1 for MNIST, batch size for NER); without ``--fast-stat-sync`` the logged loss and the
+``sample_size`` are those of the last local micro-batch; every rank seeds dropout with ``seed + num_updates``; the
+first update runs with ``lr = 0`` when warm-up is enabled.
+"""
+from __future__ import annotations
+
+import contextlib
+import math
+import os
+from collections import OrderedDict
+from itertools import chain
+from typing import Any, Dict, List, Optional
+
+import torch
+
+from . import checkpoint_utils, distributed_utils, lr_scheduler as lr_sched, optim, utils
+from .meters import AverageMeter, StopwatchMeter, TimeMeter
+from .parallel.arena import ParamArena
+from .parallel.reducer import build_reducer
+
+_LN2 = math.log(2.0)
+
+
+class _StatsMailbox:
+    """Ring of pinned host slots receiving [loss_sum, nll_sum, sample_size, nsentences, ntokens, gnorm, clipped]
+    from the device without blocking the host."""
+
+    FIELDS = 8
+
+    def __init__(self, device, depth: int = 4):
+        self.device = device
+        self.cuda = device.type == "cuda"
+        self.depth = depth
+        self.slots = [torch.zeros(self.FIELDS, dtype=torch.float64).pin_memory() if self.cuda
+                      else torch.zeros(self.FIELDS, dtype=torch.float64) for _ in range(depth)]
+        self.events = [torch.cuda.Event() if self.cuda else None for _ in range(depth)]
+        self.pending: List[int] = []
+        self.head = 0
+
+    def post(self, dev_vec: torch.Tensor) -> None:
+        i = self.head % self.depth
+        self.head += 1
+        self.slots[i].copy_(dev_vec, non_blocking=True)
+        if self.cuda:
+            self.events[i].record()
+        self.pending.append(i)
+
+    def drain(self, keep_latest: int = 0):
+        """Yield completed slots, oldest first, leaving at most ``keep_latest`` in flight."""
+        while len(self.pending) > keep_latest:
+            i = self.pending.pop(0)
+            if self.cuda:
+                self.events[i].synchronize()
+            yield self.slots[i].clone()
+
+
+class Controller:
+    def __init__(self, args, task, model, criterion=None, dummy_batch=None, oom_batch=None):
+        self.args = args
+        self.task = task
+        self.cuda = torch.cuda.is_available() and not getattr(args, "cpu", False)
+        self.device = torch.device("cuda", torch.cuda.current_device()) if self.cuda else torch.device("cpu")
+        self._model = model.to(self.device)
+        self._dummy_batch = dummy_batch
+        self._oom_batch = oom_batch or dummy_batch
+        self._lr_scheduler = None
+        self._optimizer = None
+        self._num_updates = 0
+        self._optim_history = None
+        self._prev_grad_norm = None
+        self._arena: Optional[ParamArena] = None
+        self._reducer = None
+        self.fast_stat_sync = getattr(args, "fast_stat_sync", False)
+        self.world_size = getattr(args, "distributed_world_size", 1) or 1
+        self.precision = getattr(args, "precision", "tf32")
+        if not self.cuda and self.precision == "bf16":
+            self.precision = "fp32"
+        if getattr(args, "use_bmuf", False):
+            print("| WARNING: --use-bmuf is accepted for compatibility but BMUF is not implemented; "
+                  "running synchronous data parallel")
+        self._mailbox = _StatsMailbox(self.device)
+        self._lazy_stats = self.cuda and not getattr(args, "sync_stats", False)
+        self._last_logging_output: Optional[Dict[str, Any]] = None
+        self.init_meters(args)
+
+    # ------------------------------------------------------------------------------------------------
+    def init_meters(self, args):
+        m = OrderedDict()
+        for name in ("train_loss", "train_nll_loss", "valid_loss", "valid_nll_loss"):
+            m[name] = AverageMeter()
+        m["wps"] = TimeMeter()        # words per second
+        m["ups"] = TimeMeter()        # updates per second
+        m["wpb"] = AverageMeter()     # words per batch
+        m["bsz"] = AverageMeter()     # sentences per batch
+        m["gnorm"] = AverageMeter()   # gradient norm
+        m["clip"] = AverageMeter()    # fraction of updates clipped
+        m["wall"] = TimeMeter()       # wall time in seconds
+        m["train_wall"] = StopwatchMeter()
+        self.meters = m
+
+    # ---- lazily built engine pieces -----------------------------------------------------------------
+    def _build_engine(self):
+        model = self._model
+        compute_dtype = torch.bfloat16 if self.precision == "bf16" else torch.float32
+        params = [p for p in model.parameters() if p.requires_grad]
+        groups = model.arena_groups() if hasattr(model, "arena_groups") else None
+        bucket_bytes = int(getattr(self.args, "bucket_cap_mb", 25)) * 1024 * 1024
+        self._arena = ParamArena(params, groups=groups, device=self.device, compute_dtype=compute_dtype,
+                                 bucket_bytes=bucket_bytes)
+        self._reducer = build_reducer(self.args, self._arena, self.world_size)
+        use_native = self.cuda and not getattr(self.args, "no_native", False) and self.precision != "fp32"
+        if hasattr(model, "bind_arena"):
+            model.bind_arena(self._arena if use_native else None, self._reducer)
+        if not use_native and hasattr(model, "force_torch_path"):
+            model.force_torch_path = True
+        self._hook_handles = []
+        if self.world_size > 1:
+            # parameters that plain autograd (not a native block) produces gradients for announce themselves
+            for p in self._arena.params:
+                self._hook_handles.append(p.register_post_accumulate_grad_hook(lambda q: self._reducer.ready([q])))
+            self._reducer.broadcast_parameters()
+        if self.cuda:
+            torch.backends.cuda.matmul.allow_tf32 = self.precision in ("tf32", "bf16")
+            torch.backends.cudnn.allow_tf32 = self.precision in ("tf32", "bf16")
+
+    @property
+    def arena(self) -> ParamArena:
+        if self._arena is None:
+            self._build_engine()
+        return self._arena
+
+    @property
+    def reducer(self):
+        if self._arena is None:
+            self._build_engine()
+        return self._reducer
+
+    @property
+    def model(self):
+        if self._arena is None:
+            self._build_engine()
+        return self._model
+
+    @property
+    def optimizer(self):
+        if self._optimizer is None:
+            self._build_optimizer()
+        return self._optimizer
+
+    @property
+    def lr_scheduler(self):
+        if self._lr_scheduler is None:
+            self._build_optimizer()
+        return self._lr_scheduler
+
+    def _build_optimizer(self):
+        arena = self.arena
+        self._optimizer = optim.build_optimizer(self.args, arena.params)
+        self._optimizer.attach_arena(arena)
+        self._lr_scheduler = lr_sched.build_lr_scheduler(self.args, self._optimizer)
+        self._lr_scheduler.step_update(0)
+
+    # ---- checkpoints ---------------------------------------------------------------------------------
+    def _meters_state(self):
+        return {k: {"type": type(v).__name__, "state": v.state_dict()} for k, v in self.meters.items()}
+
+    def save_checkpoint(self, filename, extra_state):
+        """Write all training state (master rank only)."""
+        self.flush_stats()
+        if distributed_utils.is_master(self.args):
+            extra_state = dict(extra_state)
+            extra_state["train_meters"] = self._meters_state()
+            checkpoint_utils.save_state(filename, self.args, self._export_model_state(), None, self.optimizer,
+                                        self.lr_scheduler, self.get_num_updates(), self._optim_history, extra_state)
+
+    def _export_model_state(self):
+        """fp32 state dict from the master weights (bf16 mode keeps a bf16 working copy in ``p.data``)."""
+        sd = self.get_model().state_dict()
+        if self._arena is not None and self._arena.work is not None:
+            named = dict(self.get_model().named_parameters())
+            for k in list(sd.keys()):
+                p = named.get(k)
+                if p is not None and hasattr(p, "master"):
+                    sd[k] = p.master
+        return sd
+
+    def load_checkpoint(self, filename, reset_optimizer=False, reset_lr_scheduler=False, optimizer_overrides=None,
+                        reset_meters=False):
+        """Restore model / optimizer / scheduler / meters; returns the checkpoint's ``extra_state`` (or None)."""
+        extra_state, self._optim_history, last_optim_state = None, [], None
+        if os.path.exists(filename):
+            state = checkpoint_utils.load_checkpoint_to_cpu(filename)
+            _ = self.arena   # parameters must already be arena views so that loading writes into the arena
+            try:
+                self.get_model().load_state_dict(state["model"], strict=True)
+            except Exception:
+                raise Exception("Cannot load model parameters from checkpoint {}; please ensure that the "
+                                "architectures match.".format(filename))
+            if self._arena.work is not None:
+                named = dict(self.get_model().named_parameters())
+                with torch.no_grad():
+                    for k, v in state["model"].items():
+                        if k in named and hasattr(named[k], "master"):
+                            named[k].master.copy_(v.to(self.device, torch.float32))
+                self._arena.sync_work_from_master()
+            extra_state = state.get("extra_state") or {}
+            self._optim_history = state["optimizer_history"]
+            last_optim_state = state.get("last_optimizer_state", None)
+
+        if last_optim_state is not None and not reset_optimizer:
+            self._build_optimizer()
+            last_optim = self._optim_history[-1]
+            assert last_optim["optimizer_name"] == self.optimizer.__class__.__name__, \
+                "Optimizer does not match; please reset the optimizer (--reset-optimizer)."
+            if not reset_lr_scheduler:
+                self.lr_scheduler.load_state_dict(last_optim["lr_scheduler_state"])
+            self.optimizer.load_state_dict(last_optim_state, optimizer_overrides)
+            self.set_num_updates(last_optim["num_updates"])
+
+        if extra_state is not None:
+            epoch = extra_state.get("train_iterator", {}).get("epoch", 0)
+            print("| loaded checkpoint {} (epoch {} @ {} updates)".format(filename, epoch, self.get_num_updates()))
+            self.lr_step(epoch)
+            tm = extra_state.pop("train_meters", None)
+            if tm is not None and not reset_meters:
+                for k, rec in tm.items():
+                    if k in self.meters and isinstance(rec, dict) and "state" in rec:
+                        self.meters[k].load_state_dict(rec["state"])
+                for meter in self.meters.values():
+                    if isinstance(meter, TimeMeter):
+                        meter.reset()
+        else:
+            print("| no existing checkpoint found {}".format(filename))
+        return extra_state
+
+    # ---- data -----------------------------------------------------------------------------------------
+    def get_train_iterator(self, epoch, combine=True, load_dataset=True):
+        if load_dataset:
+            print("| loading train data for epoch {}".format(epoch))
+            self.task.load_dataset(self.args.train_subset)
+        return self.task.get_batch_iterator(
+            dataset=self.task.dataset(self.args.train_subset), max_tokens=self.args.max_tokens,
+            max_sentences=self.args.max_sentences, max_positions=None, ignore_invalid_inputs=True,
+            required_batch_size_multiple=self.args.required_batch_size_multiple, seed=self.args.seed,
+            num_shards=self.world_size, shard_id=getattr(self.args, "distributed_rank", 0) or 0,
+            num_workers=self.args.num_workers, epoch=epoch)
+
+    def _prepare_sample(self, sample):
+        if utils.sample_is_empty(sample):
+            return None
+        if self.cuda:
+            sample = utils.move_to_cuda(sample, self.device, non_blocking=True)
+        return sample
+
+    def _set_seed(self):
+        seed = self.args.seed + self.get_num_updates()
+        torch.manual_seed(seed)
+        if self.cuda:
+            torch.cuda.manual_seed(seed)
+            from .ops import kernels
+            kernels.Workspace.get(self.device).set_seed(seed)
+
+    # ---- the hot loop -----------------------------------------------------------------------------------
+    def train_step(self, samples, dummy_batch=False, raise_oom=False):
+        """Forward, backward, cross-rank reduction and parameter update for one group of micro-batches."""
+        if self._dummy_batch is None:
+            self._dummy_batch = samples[0]
+        model, optimizer, reducer = self.model, self.optimizer, self.reducer
+        self._set_seed()
+        model.train()
+        if not dummy_batch:
+            self.meters["train_wall"].start()
+
+        dev = self.device
+        stat_sum = torch.zeros(self._mailbox.FIELDS, dtype=torch.float64, device=dev)
+        host_stats = [0.0] * 5            # sample_size, nsentences, ntokens, (last) sample_size, n_real
+        last_logging, last_sample_size = None, 0
+        for i, sample in enumerate(samples):
+            sample = self._prepare_sample(sample)
+            ignore_grad = sample is None
+            if ignore_grad:
+                # short rank at the end of an epoch: stay in lock-step with a zero-weight batch
+                sample = self._prepare_sample(self._dummy_batch)
+            reducer.begin(sync_now=(i == len(samples) - 1))
+            try:
+                loss, sample_size, logging_output = self.task.train_step(sample, model, optimizer, ignore_grad)
+            except RuntimeError as e:
+                if "out of memory" in str(e):
+                    raise RuntimeError("ran out of memory with exception: {}".format(e))
+                raise
+            if not ignore_grad:
+                host_stats[0] += sample_size
+                host_stats[1] += logging_output.get("nsentences", 0)
+                host_stats[2] += logging_output.get("ntokens", 0)
+                stat_sum[0] += _as_dev_scalar(logging_output.get("loss", 0.0), dev)
+                stat_sum[1] += _as_dev_scalar(logging_output.get("nll_loss", 0.0), dev)
+                last_logging, last_sample_size = logging_output, sample_size
+        reducer.finish()
+        if dummy_batch:
+            return None
+
+        # ---- statistics -----------------------------------------------------------------------------------
+        sample_size_dev = None
+        if self.fast_stat_sync:
+            stat_sum[2:5] += torch.tensor(host_stats[:3], dtype=torch.float64).to(dev, non_blocking=True)
+            if self.world_size > 1:
+                torch.distributed.all_reduce(stat_sum[:5])
+            sample_size_dev = stat_sum[2:3]
+            sample_size = None                     # lives on the device
+        else:
+            if self.world_size > 1:
+                gathered = distributed_utils.all_gather_list([host_stats[:3], self._prev_grad_norm_host()])
+                norms = [g[1] for g in gathered]
+                if not getattr(self.args, "use_bmuf", False):
+                    assert all(n == norms[0] for n in norms) or all(n is None or math.isnan(n) or math.isinf(n) for n in norms), \
+                        "Fatal error: gradients are inconsistent between workers"
+            sample_size = last_sample_size
+            stat_sum[2:5] = torch.tensor([float(last_sample_size), float((last_logging or {}).get("nsentences", 0)),
+                                          float((last_logging or {}).get("ntokens", 0))], dtype=torch.float64).to(dev, non_blocking=True)
+            if last_logging is not None:
+                stat_sum[0] = _as_dev_scalar(last_logging.get("loss", 0.0), dev)
+                stat_sum[1] = _as_dev_scalar(last_logging.get("nll_loss", 0.0), dev)
+
+        # ---- scale, clip, update: one fused kernel on the arena -------------------------------------------
+        clip_norm = float(getattr(self.args, "clip_norm", 0.0))
+        if self.cuda:
+            from .ops import kernels
+            ws = kernels.Workspace.get(dev)
+            kernels.sumsq(self._arena.grad, ws.norm_sq, ws=ws)
+            if sample_size_dev is not None:
+                mult, ss_dev = 1.0, sample_size_dev
+            else:
+                mult, ss_dev = (1.0 / float(sample_size) if sample_size and sample_size > 0 else 1.0), None
+            optimizer.optimizer.fused_step(grad_scale_mult=mult, max_norm=clip_norm, norm_sq=ws.norm_sq,
+                                           sample_size=ss_dev, stats_out=ws.step_stats, zero_grad=True)
+            stat_sum[5:7] = ws.step_stats[0:3:2].double()
+        else:
+            if sample_size_dev is not None:
+                ss = float(sample_size_dev.item())
+            else:
+                ss = float(sample_size)
+            if ss > 0:
+                optimizer.multiply_grads(1.0 / ss)
+            gnorm = optimizer.clip_grad_norm(clip_norm)
+            optimizer.step()
+            optimizer.zero_grad()
+            stat_sum[5] = float(gnorm)
+            stat_sum[6] = 1.0 if (clip_norm > 0 and float(gnorm) > clip_norm) else 0.0
+
+        self.set_num_updates(self.get_num_updates() + 1)
+        self.task.update_step(self._num_updates)
+
+        # ---- meters (asynchronously on CUDA) --------------------------------------------------------------
+        self._mailbox.post(stat_sum)
+        self._consume_stats(keep_latest=1 if self._lazy_stats else 0)
+        self.meters["train_wall"].stop()
+        return self._last_logging_output if self._last_logging_output is not None else {
+            "loss": 0.0, "nll_loss": 0.0, "ntokens": 0, "nsentences": 0, "sample_size": 0}
+
+    def _prev_grad_norm_host(self):
+        return self._prev_grad_norm
+
+    def _consume_stats(self, keep_latest: int):
+        for v in self._mailbox.drain(keep_latest):
+            loss, nll, sample_size, nsent, ntok, gnorm, clipped = (float(x) for x in v[:7])
+            if self.fast_stat_sync and sample_size > 0:
+                # reference: global sums divided by sample_size and converted to base 2 (controller.py:298-305)
+                loss, nll = loss / (sample_size * _LN2), nll / (sample_size * _LN2)
+            self._prev_grad_norm = gnorm
+            m = self.meters
+            m["wps"].update(ntok)
+            m["ups"].update(1.0)
+            m["wpb"].update(ntok)
+            m["bsz"].update(nsent)
+            m["gnorm"].update(gnorm)
+            m["clip"].update(clipped)
+            m["train_loss"].update(loss, sample_size)
+            self._last_logging_output = {"loss": loss, "nll_loss": nll, "ntokens": ntok, "nsentences": nsent,
+                                         "sample_size": sample_size, "gnorm": gnorm}
+
+    def flush_stats(self):
+        """Block until every posted step has reached the meters."""
+        self._consume_stats(keep_latest=0)
+
+    @torch.no_grad()
+    def valid_step(self, sample, raise_oom=False):
+        """Forward only; returns ``{'loss', 'sample_size', 'nsentences', 'ntokens'}`` summed over ranks."""
+        model = self.model
+        model.eval()
+        sample = self._prepare_sample(sample)
+        ignore = sample is None
+        if ignore:
+            sample = self._prepare_sample(self._dummy_batch)
+        loss, sample_size, logging_output = self.task.valid_step(sample, model)
+        vec = torch.zeros(4, dtype=torch.float64, device=self.device)
+        if not ignore:
+            vec[0] = _as_dev_scalar(logging_output.get("loss", 0.0), self.device) * sample_size
+            vec[1:4] = torch.tensor([float(sample_size), float(logging_output.get("nsentences", 0)),
+                                     float(logging_output.get("ntokens", 0))], dtype=torch.float64).to(self.device)
+        if self.world_size > 1:
+            torch.distributed.all_reduce(vec)
+        tot, ss, ns, nt = vec.tolist()
+        out = {"loss": tot / ss if ss > 0 else 0.0, "sample_size": ss, "nsentences": ns, "ntokens": nt}
+        if ss > 0:
+            self.meters["valid_loss"].update(out["loss"], ss)
+        return out
+
+    # ---- small accessors --------------------------------------------------------------------------------
+    def zero_grad(self):
+        self.optimizer.zero_grad()
+
+    def lr_step(self, epoch, val_loss=None):
+        self.lr_scheduler.step(epoch, val_loss)
+        return self.lr_step_update()
+
+    def lr_step_update(self):
+        return self.lr_scheduler.step_update(self.get_num_updates())
+
+    def get_lr(self):
+        return self.optimizer.get_lr()
+
+    def get_model(self):
+        return self._model
+
+    def get_meter(self, name):
+        return self.meters.get(name)
+
+    def get_num_updates(self):
+        return self._num_updates
+
+    def set_num_updates(self, num_updates):
+        self._num_updates = num_updates
+        self.lr_step_update()
+
+
+def _as_dev_scalar(x, device) -> torch.Tensor:
+    if torch.is_tensor(x):
+        return x.detach().reshape(()).to(device=device, dtype=torch.float64)
+    return torch.tensor(float(x), dtype=torch.float64, device=device)

@@ -1,0 +1,138 @@
+"""Data-parallel gradient reduction over the flat gradient arena.
+
+The reference delegates this to ``torch.nn.parallel.DistributedDataParallel`` (hetseq/controller.py:75-90): its
+Reducer copies gradients into 25 MB buckets, all-reduces each with NCCL, divides by the world size and copies
+back.  Here gradients already live in one flat fp32 buffer, buckets are slices of it, and a reducer is a
+``GradSink``: backward code tells it which parameters are final and it launches the reduction of a bucket as
+soon as all of the bucket's parameters are in, on a side stream, while backward keeps running.
+
+Two back ends:
+
+* ``TorchReducer`` — ``torch.distributed.all_reduce(SUM)`` per bucket (NCCL on GPUs, gloo on CPU).  The baseline
+  and the portable path (multi-node, CPU tests).
+* ``P2PReducer`` (``parallel/p2p.py``) — hand-written sm_100a kernels that read and write the peers' arenas
+  directly over NVLink (two-shot reduce-scatter + all-gather, one-shot for small buckets).
+
+Both produce the SUM over ranks; the 1/sample_size scale and the clip coefficient are applied inside the fused
+optimizer kernel, so no separate "divide by world size" pass exists.
+"""
+from __future__ import annotations
+
+from typing import Dict, List, Optional
+
+import torch
+import torch.distributed as dist
+
+from ..models.bert_native import GradSink
+
+
+class BaseReducer(GradSink):
+    def __init__(self, arena, world_size: int):
+        self.arena = arena
+        self.world_size = world_size
+        self._pending: List[int] = []
+        self._remaining: Dict[int, int] = {}
+        self._active = False
+        self._expected = {bi: len({id(p) for p in ms}) for bi, (_, _, ms) in enumerate(arena.buckets)}
+        self._seen = set()
+        self.exposed_ms = 0.0
+
+    # ---- step protocol ---------------------------------------------------------------------------
+    def begin(self, sync_now: bool):
+        """Called before each micro-batch's backward; ``sync_now`` is True only for the last one."""
+        self._active = sync_now and self.world_size > 1
+        self._remaining = dict(self._expected)
+        self._seen = set()
+        self._launched = set()
+
+    def ready(self, params) -> None:
+        if not self._active:
+            return
+        for p in params:
+            pid = id(p)
+            if pid in self._seen or pid not in self.arena.bucket_of:
+                continue
+            self._seen.add(pid)
+            bi = self.arena.bucket_of[pid]
+            self._remaining[bi] -= 1
+            if self._remaining[bi] == 0:
+                self._launch(bi)
+
+    def finish(self):
+        """After backward: reduce whatever was not announced (unused parameters, torch-autograd-only models),
+        then make the training stream wait for all reductions."""
+        if self._active:
+            for bi in range(len(self.arena.buckets)):
+                if bi not in self._launched:
+                    self._launch(bi)
+            self._wait_all()
+        self._active = False
+
+    # ---- back-end hooks --------------------------------------------------------------------------
+    def _launch(self, bucket_index: int):
+        raise NotImplementedError
+
+    def _wait_all(self):
+        raise NotImplementedError
+
+    def broadcast_parameters(self):
+        """Make every rank start from rank 0's parameters (what DDP does at construction)."""
+        if self.world_size > 1:
+            dist.broadcast(self.arena.master, src=0)
+            if self.arena.work is not None:
+                self.arena.sync_work_from_master()
+
+
+class TorchReducer(BaseReducer):
+    def __init__(self, arena, world_size: int, group=None):
+        super().__init__(arena, world_size)
+        self.group = group
+        self._works = []
+        self._cuda = arena.device.type == "cuda"
+        self._side = torch.cuda.Stream(device=arena.device) if self._cuda else None
+
+    def _launch(self, bi: int):
+        self._launched.add(bi)
+        s, e, _ = self.arena.buckets[bi]
+        view = self.arena.grad[s:e]
+        if self._cuda:
+            ev = torch.cuda.Event()
+            ev.record(torch.cuda.current_stream())
+            with torch.cuda.stream(self._side):
+                self._side.wait_event(ev)
+                self._works.append(dist.all_reduce(view, group=self.group, async_op=True))
+        else:
+            self._works.append(dist.all_reduce(view, group=self.group, async_op=True))
+
+    def _wait_all(self):
+        for w in self._works:
+            w.wait()
+        self._works = []
+        if self._cuda:
+            torch.cuda.current_stream().wait_stream(self._side)
+
+
+class NullReducer(BaseReducer):
+    """world_size == 1."""
+
+    def _launch(self, bi):
+        self._launched.add(bi)
+
+    def _wait_all(self):
+        pass
+
+
+def build_reducer(args, arena, world_size: int):
+    if world_size <= 1:
+        return NullReducer(arena, 1)
+    comm = getattr(args, "comm", "auto")
+    if arena.device.type == "cuda" and comm in ("auto", "p2p"):
+        try:
+            from .p2p import P2PReducer
+            return P2PReducer(arena, world_size)
+        except Exception as e:  # peer access unavailable (multi-node, MIG, ...) -> documented fallback
+            if comm == "p2p":
+                raise
+            from ..distributed_utils import log_all
+            log_all("| p2p reducer unavailable ({}); using torch.distributed all-reduce".format(e))
+    return TorchReducer(arena, world_size)

@@ -1,0 +1,148 @@
+"""Reference arm of bench.py: runs the UNMODIFIED reference installed in ``baseline/_ref`` (pip --no-deps
+--target) through its own public API and stock code path —
+``tasks.LanguageModelingTask`` -> ``Controller`` (DistributedDataParallel + NCCL) -> ``controller.train_step`` driven by
+its own ``EpochBatchIterator`` / ``GroupedIterator`` exactly as its ``train()`` does — on the same synthetic corpus,
+model config, batch size and optimizer flags as our arm.  None of this framework's models, kernels or engine
+are on that path; the only additions are import stubs for packages the image lacks (``baseline/shims``: h5py
+backed by .npz, boto3/botocore) and ``sys.path`` entries the reference needs (it imports its own modules by
+bare name, e.g. hetseq/checkpoint_utils.py:15, hetseq/data/data_utils.py:50)."""
+from __future__ import annotations
+
+import json
+import os
+import shutil
+import sys
+import tempfile
+import time
+import warnings
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+ROOT = os.path.dirname(HERE)
+REF = os.path.join(HERE, "_ref")
+
+
+def _unavailable(why):
+    print(json.dumps({"impl": "reference", "unavailable": why}), flush=True)
+    return 0
+
+
+def run_reference(a):
+    if not os.path.isdir(os.path.join(REF, "hetseq")):
+        return _unavailable("baseline/_ref is missing (pip install --no-deps --target baseline/_ref /root/reference)")
+    try:
+        import torch
+    except Exception as e:
+        return _unavailable("torch import failed: %s" % e)
+    if not torch.cuda.is_available():
+        return _unavailable("no CUDA device visible (the reference's Controller is CUDA-only)")
+    warnings.filterwarnings("ignore")
+    sys.path.insert(0, os.path.join(HERE, "shims"))
+    sys.path.insert(0, REF)
+    sys.path.insert(0, os.path.join(REF, "hetseq"))
+    sys.path.insert(0, ROOT)
+    import numpy as np
+    import torch.distributed as dist
+    from bench import ClockSampler, MODELS, PUBLISHED_SEQ_PER_SEC_PER_GPU
+    from hetseq_9cme_b200.data import synthetic   # data *generation* only (same arrays as our arm)
+
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    torch.cuda.set_device(local)
+    try:
+        from hetseq import options, tasks, distributed_utils
+        from hetseq.controller import Controller
+        from hetseq.data import iterators
+    except Exception as e:
+        return _unavailable("reference import failed: %r" % (e,))
+
+    tmp = tempfile.mkdtemp(prefix="refbench_r%d_" % rank)
+    try:
+        nsteps_needed = a.steps + a.warmup + 4
+        per_rank = nsteps_needed * a.batch
+        max_pred = 20 if a.seq_len <= 128 else 80
+        n_per_file = (per_rank * world + 1) // 2 + a.batch
+        for i in range(2):
+            arrs = synthetic.bert_shard_arrays(n_per_file, a.seq_len, max_pred, 30522, 1234 + i)
+            np.savez(os.path.join(tmp, "train_shard_%d.npz" % i), **arrs)
+        np.savez(os.path.join(tmp, "test_shard_0.npz"), **synthetic.bert_shard_arrays(a.batch, a.seq_len, max_pred, 30522, 2234))
+        cfg_path = synthetic.write_bert_config(os.path.join(tmp, "bert_config.json"), **MODELS[a.model])
+        vocab_path = synthetic.write_vocab(os.path.join(tmp, "vocab.txt"))
+        argv = ["--data", tmp, "--dict", vocab_path, "--config_file", cfg_path, "--max-sentences", str(a.batch),
+                "--max-epoch", "1000", "--lr", "1e-4", "--warmup-updates", "100", "--total-num-update", "100000",
+                "--weight-decay", "0.01", "--clip-norm", "25", "--fast-stat-sync", "--valid-subset", "test", "--num-workers", "4",
+                "--save-dir", os.path.join(tmp, "ckpt"), "--no-save", "--log-format", "none",
+                "--distributed-world-size", str(world)]
+        parser = options.get_training_parser(task="bert", optimizer="adam", lr_scheduler="PolynomialDecayScheduler")
+        args = options.parse_args_and_arch(parser, argv)
+        args.device_id = local
+        args.distributed_rank = rank
+        np.random.seed(args.seed)
+        torch.manual_seed(args.seed)
+        if world > 1:
+            args.distributed_init_method = "env://"
+            args.distributed_rank = distributed_utils.distributed_init(args)
+        task = tasks.LanguageModelingTask.setup_task(args)
+        task.load_dataset("test", combine=False, epoch=0)
+        model = task.build_model(args)
+        controller = Controller(args, task, model)
+        epoch_itr = controller.get_train_iterator(epoch=0, load_dataset=True)
+        controller.lr_step(epoch_itr.epoch)
+        itr = epoch_itr.next_epoch_itr(shuffle=True)
+        itr = iterators.GroupedIterator(itr, 1)
+
+        def sync_all():
+            torch.cuda.synchronize()
+            if world > 1:
+                dist.barrier()
+                torch.cuda.synchronize()
+
+        for _ in range(a.warmup):
+            controller.train_step(next(itr))
+        sync_all()
+        sampler = ClockSampler(local)
+        sampler.start()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        h2d = 0
+        t0 = time.perf_counter()
+        e0.record()
+        for _ in range(a.steps):
+            samples = next(itr)
+            h2d += sum(t.numel() * t.element_size() for t in samples[0])
+            controller.train_step(samples)
+        e1.record()
+        sync_all()
+        wall_ms = (time.perf_counter() - t0) * 1e3
+        dev_ms = e0.elapsed_time(e1)
+        clocks = sampler.stop()
+        t = torch.tensor([dev_ms, wall_ms], device="cuda", dtype=torch.float64)
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        dev_ms, wall_ms = t.tolist()
+        gb = a.batch * world
+        value = gb * a.steps / (dev_ms / 1e3)
+        out = {"metric": "BERT-base phase-1 pre-training throughput (seq 128)", "value": round(value, 2), "unit": "sequences/s",
+               "n_gpus": world, "steps": a.steps, "warmup": a.warmup, "ms_per_step": round(dev_ms / a.steps, 4),
+               "higher_is_better": True, "scaling": "weak", "vs_baseline": round(value / (PUBLISHED_SEQ_PER_SEC_PER_GPU * world), 2),
+               "dtype": "fp32", "data": "synthetic", "impl": "reference",
+               "config": {"model": a.model, "global_batch": gb, "per_gpu_batch": a.batch, "seq_len": a.seq_len,
+                          "parallelism": "dp%d" % world, "allow_tf32": bool(torch.backends.cuda.matmul.allow_tf32),
+                          "path": "hetseq.controller.Controller.train_step (DDP + NCCL + cuBLAS), unmodified",
+                          "timing": "CUDA events around the K public-API steps incl. their H2D copies and host syncs; max over ranks"},
+               "clocks": clocks,
+               "e2e": {"value": round(gb * a.steps / (wall_ms / 1e3), 2), "unit": "sequences/s",
+                       "ms_per_step": round(wall_ms / a.steps, 4), "h2d_bytes_per_step": int(h2d / a.steps),
+                       "d2h_bytes_per_step": 48},
+               "gpu_launches": 0}
+        if rank == 0 or world == 1:
+            sys.__stdout__.write(json.dumps(out) + "\n")
+            sys.__stdout__.flush()
+        if world > 1:
+            dist.barrier()
+    except Exception as e:
+        import traceback
+        traceback.print_exc(file=sys.stderr)
+        return _unavailable("reference run failed: %r" % (e,))
+    finally:
+        shutil.rmtree(tmp, ignore_errors=True)
+    return 0

@@ -9,6 +9,7 @@
 #include "../include/b200seq.h"
 
 #include <cfloat>
+#include <mutex>
 
 namespace b200 {
 
@@ -647,5 +648,77 @@ extern "C" int b200_act_bwd(int dtype, const void* dy, const void* aux, void* ou
   if (blocks < 1) blocks = 1;
   DISPATCH_T(dtype, (act_bwd_kernel<T><<<(int)blocks, 256, 0, (cudaStream_t)stream>>>((const T*)dy, (const T*)aux, (T*)out, n, mode)));
   B200_LAUNCHED("act_bwd_kernel");
+  return 0;
+}
+
+// ------------------------------------------------------------------------------------------------------------
+// b200_colsum_static: the same column sum as b200_colsum, for callers that must not allocate device memory.
+//
+// Who that is: a host program that has already handed the whole device to its own pool allocator (a
+// cudaMalloc from inside this library would simply fail, or fragment the pool), and a latency-sensitive loop
+// that cannot afford the device-wide synchronisation cudaMalloc / cudaFree imply.  Such a caller also cannot
+// hand us a scratch buffer it never planned for, so the per-block partial sums live in a fixed array that is
+// part of the library image: kStaticColsumParts x kStaticColsumMaxCols floats = 1 MiB.  Every GPU that loads
+// the library keeps that 1 MiB resident until the process exits, whether or not this entry point is used.
+//
+// `g_colsum_static_scratch` below is a __device__ symbol.  In host code that name is only a handle for the
+// runtime, not a device address — passing it to a kernel directly would fault (or, where the GPU can reach host
+// memory, quietly scribble over host memory).  The address the kernels receive therefore comes from
+// cudaGetSymbolAddress, looked up once per device with that device current; the first call on each device does
+// this set-up (it is a host-side lookup, no allocation).  Make that first call before starting any stream
+// capture, so the lookup never lands inside a capture.
+//
+// The array is shared by every call and keeps whatever the previous call left in it.  Nothing in it has to be
+// zero beforehand: each launch overwrites every partial it later reads.  Because it is shared, two calls that
+// can run on the GPU at the same time (different streams, different host threads) race on it — issue them on
+// one stream or order them with events.
+// ------------------------------------------------------------------------------------------------------------
+namespace b200 {
+constexpr int kStaticColsumParts = 64;
+constexpr int kStaticColsumMaxCols = 4096;
+static __device__ __align__(256) float g_colsum_static_scratch[kStaticColsumParts * kStaticColsumMaxCols];
+
+constexpr int kMaxDevices = 64;
+static float* g_colsum_static_ptr[kMaxDevices] = {nullptr};
+static std::mutex g_colsum_static_mu;
+
+// device address of the static scratch on the current device (looked up once per device)
+static int colsum_static_scratch(float** out) {
+  int dev = -1;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) return cuda_fail(e, "colsum_static: cudaGetDevice");
+  if (dev < 0 || dev >= kMaxDevices) return fail(B200_ERR_UNSUPPORTED, "colsum_static: device ordinal %d out of range", dev);
+  std::lock_guard<std::mutex> lock(g_colsum_static_mu);
+  if (g_colsum_static_ptr[dev] == nullptr) {
+    float* p = nullptr;
+    e = cudaGetSymbolAddress(reinterpret_cast<void**>(&p), g_colsum_static_scratch);
+    if (e != cudaSuccess) return cuda_fail(e, "colsum_static: cudaGetSymbolAddress");
+    if (p == nullptr) return fail(B200_ERR_STATE, "colsum_static: symbol address is null");
+    g_colsum_static_ptr[dev] = p;
+  }
+  *out = g_colsum_static_ptr[dev];
+  return 0;
+}
+}  // namespace b200
+
+extern "C" int b200_colsum_static_max_cols(void) { return b200::kStaticColsumMaxCols; }
+
+extern "C" int b200_colsum_static(int dtype, const void* x, long long ldx, int rows, int cols, float* out, void* stream) {
+  if (!x || !out) return fail(B200_ERR_ARG, "colsum_static: null pointer");
+  if (rows <= 0 || cols <= 0) return fail(B200_ERR_ARG, "colsum_static: empty input (%d x %d)", rows, cols);
+  if (cols & 3) return fail(B200_ERR_UNSUPPORTED, "colsum_static: cols must be a multiple of 4");
+  if (cols > kStaticColsumMaxCols)
+    return fail(B200_ERR_ARG, "colsum_static: cols = %d exceeds the built-in scratch (max %d columns); use b200_colsum with your own scratch",
+                cols, kStaticColsumMaxCols);
+  float* scratch = nullptr;
+  const int rc = colsum_static_scratch(&scratch);
+  if (rc) return rc;
+  const int parts = rows >= 2048 ? kStaticColsumParts : (rows >= 256 ? 16 : 1);
+  const int rpb = (rows + parts - 1) / parts;
+  dim3 grid((cols + 1023) / 1024, parts);
+  DISPATCH_T(dtype, (colsum_partial_kernel<T><<<grid, 256, 0, (cudaStream_t)stream>>>((const T*)x, ldx, rows, cols, rpb, scratch)));
+  B200_LAUNCHED("colsum_partial_kernel(static)");
+  colsum_final_kernel<<<(cols + 255) / 256, 256, 0, (cudaStream_t)stream>>>(scratch, parts, cols, out);
+  B200_LAUNCHED("colsum_final_kernel(static)");
   return 0;
 }

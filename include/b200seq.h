@@ -171,6 +171,18 @@ int b200_dropout(int dtype, const void* x, void* y, long long n, float p, const 
 long long b200_colsum_scratch_bytes(int rows, int cols);
 int b200_colsum(int dtype, const void* x, long long ldx, int rows, int cols, float* out, void* scratch,
                 long long scratch_bytes, void* stream);
+/* Same result as b200_colsum (out[c] += sum_r x[r][c]) for callers that cannot allocate device memory — for
+ * instance a host application whose own pool already owns the whole device, or a loop that cannot take the
+ * device-wide stall of cudaMalloc/cudaFree — and therefore have no scratch to pass.  This entry point has no
+ * counterpart in the reference.  The partial sums go to a 1 MiB array built into the library image (resident on
+ * every GPU that loads the library, until exit); cols must be a multiple of 4 and at most
+ * b200_colsum_static_max_cols() (= 4096), larger inputs are refused with an error.  Allocates nothing.  The first
+ * call on each device resolves the array's device address (make that call before any stream capture begins).
+ * All calls share the one array and it keeps the previous call's partials (none of them needs clearing: every
+ * launch rewrites what it reads), so calls that may overlap on the GPU race — keep them on one stream or order
+ * them with events. */
+int b200_colsum_static_max_cols(void);
+int b200_colsum_static(int dtype, const void* x, long long ldx, int rows, int cols, float* out, void* stream);
 
 /* ------------------------------------------------------------------------------------------------
  * Attention softmax over scores S[B][heads][L][Lp] produced by the batched GEMM (already scaled):

@@ -95,6 +95,8 @@ def open_shard(path: str):
     if low.endswith((".hdf5", ".h5", ".hdf")):
         try:
             import h5py  # type: ignore
+            if not hasattr(h5py, "File") or not hasattr(h5py, "version"):
+                raise ImportError("h5py stub")
             with h5py.File(path, "r") as f:
                 return _DictShard({k: np.asarray(f[k][:]) for k in f.keys()})
         except ImportError:

@@ -19,8 +19,9 @@ import torch
 def bert_shard_arrays(n: int, seq_len: int = 128, max_pred: int = 20, vocab_size: int = 30522, seed: int = 0,
                       full_length: bool = True):
     rng = np.random.RandomState(seed)
-    ids = rng.randint(1000, vocab_size, size=(n, seq_len)).astype(np.int32)
-    ids[:, 0] = 101
+    low = min(1000, max(1, vocab_size // 2))
+    ids = rng.randint(low, vocab_size, size=(n, seq_len)).astype(np.int32)
+    ids[:, 0] = min(101, vocab_size - 1)
     lens = np.full(n, seq_len) if full_length else rng.randint(seq_len // 2, seq_len + 1, size=n)
     mask = (np.arange(seq_len)[None, :] < lens[:, None]).astype(np.int32)
     ids *= mask
@@ -32,7 +33,7 @@ def bert_shard_arrays(n: int, seq_len: int = 128, max_pred: int = 20, vocab_size
         k = rng.randint(max(1, max_pred - 3), max_pred + 1)
         p = np.sort(rng.choice(np.arange(1, lens[r]), size=min(k, lens[r] - 1), replace=False))
         pos[r, :len(p)] = p
-        mids[r, :len(p)] = rng.randint(1000, vocab_size, size=len(p))
+        mids[r, :len(p)] = rng.randint(low, vocab_size, size=len(p))
     nsl = rng.randint(0, 2, size=n).astype(np.int32)
     return {"input_ids": ids, "input_mask": mask, "segment_ids": seg, "masked_lm_positions": pos,
             "masked_lm_ids": mids, "next_sentence_labels": nsl}

@@ -169,8 +169,9 @@ class MNISTNet(nn.Module):
         super().__init__()
         self.conv1 = nn.Conv2d(1, 32, 3, 1)
         self.conv2 = nn.Conv2d(32, 64, 3, 1)
-        self.dropout1 = nn.Dropout2d(0.25)
-        self.dropout2 = nn.Dropout(0.5)
+        no_drop = bool(os.environ.get("B200SEQ_TEST_NO_DROPOUT"))      # test hook: deterministic replicas
+        self.dropout1 = nn.Dropout2d(0.0 if no_drop else 0.25)
+        self.dropout2 = nn.Dropout(0.0 if no_drop else 0.5)
         self.fc1 = nn.Linear(9216, 128)
         self.fc2 = nn.Linear(128, 10)
 

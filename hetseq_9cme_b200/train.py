@@ -62,6 +62,8 @@ def main(args, init_distributed=False):
     print("| training on {} {}".format(args.distributed_world_size, "GPUs" if use_cuda else "CPU processes"))
     print("| max tokens per GPU = {} and max sentences per GPU = {}".format(args.max_tokens, args.max_sentences))
 
+    if hasattr(checkpoint_utils.save_checkpoint, "best"):      # per-run state (matters when main() is called twice)
+        del checkpoint_utils.save_checkpoint.best
     extra_state, epoch_itr = checkpoint_utils.load_checkpoint(args, controller)
 
     max_epoch = args.max_epoch or math.inf

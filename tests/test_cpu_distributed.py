@@ -1,0 +1,71 @@
+"""Two-process CPU/gloo runs (BASELINE config #1 — something the reference itself cannot do: its stat sync and DDP
+wrapper are CUDA-only, hetseq/controller.py:81,295)."""
+import os
+import sys
+
+import pytest
+import torch
+import torch.multiprocessing as mp
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def _worker(rank, world, port, data_dir, out_dir, fast):
+    sys.path.insert(0, ROOT)
+    from hetseq_9cme_b200 import options, train
+    argv = ["--task", "mnist", "--optimizer", "adadelta", "--data", data_dir, "--cpu", "--max-sentences", "16", "--lr", "1.0",
+            "--valid-subset", "test", "--save-dir", os.path.join(out_dir, "ckpt"), "--distributed-world-size", str(world),
+            "--distributed-backend", "gloo", "--distributed-init-method", "tcp://127.0.0.1:%d" % port,
+            "--distributed-rank", str(rank), "--num-workers", "0", "--clip-norm", "100", "--log-format", "none",
+            "--max-epoch", "1", "--no-save", "--seed", "3"] + (["--fast-stat-sync"] if fast else [])
+    args = options.parse_training_args(argv)
+    args.device_id = 0
+    c = train.main(args, init_distributed=True)
+    torch.save({k: v.clone() for k, v in c.get_model().state_dict().items()}, os.path.join(out_dir, "rank%d.pt" % rank))
+    torch.save({"updates": c.get_num_updates(), "loss": c.get_meter("train_loss").avg}, os.path.join(out_dir, "meta%d.pt" % rank))
+
+
+@pytest.mark.parametrize("fast", [False, True])
+def test_mnist_gloo_world2_ranks_stay_identical(tmp_path, fast):
+    from hetseq_9cme_b200.data import synthetic
+    from hetseq_9cme_b200.distributed_utils import find_free_port
+    d = str(tmp_path)
+    synthetic.make_mnist(d, 16 * 7, 32)         # 7 batches over 2 ranks -> rank 1 gets one dummy (lock-step) batch
+    port = find_free_port()
+    mp.spawn(_worker, args=(2, port, d, d, fast), nprocs=2, join=True)
+    a, b = torch.load(os.path.join(d, "rank0.pt")), torch.load(os.path.join(d, "rank1.pt"))
+    for k in a:
+        assert torch.equal(a[k], b[k]), k                          # replicas bit-identical after training
+    m0, m1 = torch.load(os.path.join(d, "meta0.pt")), torch.load(os.path.join(d, "meta1.pt"))
+    assert m0["updates"] == m1["updates"] == 4                     # ceil(7 / 2) steps on both ranks
+
+
+def _single(data_dir, out_dir):
+    sys.path.insert(0, ROOT)
+    from hetseq_9cme_b200 import options, train
+    argv = ["--task", "mnist", "--optimizer", "adadelta", "--data", data_dir, "--cpu", "--max-sentences", "16", "--lr", "1.0",
+            "--valid-subset", "test", "--save-dir", os.path.join(out_dir, "ckpt1"), "--distributed-world-size", "1",
+            "--num-workers", "0", "--clip-norm", "100", "--log-format", "none", "--max-epoch", "1", "--no-save", "--seed", "3",
+            "--update-freq", "2", "--fast-stat-sync"]
+    c = train.main(options.parse_training_args(argv))
+    return {k: v.clone() for k, v in c.get_model().state_dict().items()}
+
+
+def test_two_ranks_equal_one_rank_with_accumulation(tmp_path):
+    """W=2 with batch b and W=1 with --update-freq 2 see the same samples per update (batches r, r+W), so with
+    dropout disabled by eval-free determinism... the summed gradients, hence the weights, must agree closely."""
+    from hetseq_9cme_b200.data import synthetic
+    from hetseq_9cme_b200.distributed_utils import find_free_port
+    import hetseq_9cme_b200.tasks.tasks as T
+    d = str(tmp_path)
+    synthetic.make_mnist(d, 16 * 8, 32)
+    port = find_free_port()
+    os.environ["B200SEQ_TEST_NO_DROPOUT"] = "1"
+    try:
+        mp.spawn(_worker, args=(2, port, d, d, True), nprocs=2, join=True)
+        two = torch.load(os.path.join(d, "rank0.pt"))
+        one = _single(d, d)
+    finally:
+        os.environ.pop("B200SEQ_TEST_NO_DROPOUT", None)
+    for k in two:
+        assert torch.allclose(two[k], one[k], atol=2e-5), k

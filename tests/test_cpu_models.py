@@ -1,0 +1,140 @@
+"""Model-level parity on CPU: state-dict keys and losses against the reference BERT file, datasets, collators,
+NER pipeline, and a tiny BERT pre-training run through the CLI."""
+import os
+import sys
+import types
+
+import numpy as np
+import pytest
+import torch
+
+REF = "/root/reference"
+CFG = dict(hidden_size=64, num_hidden_layers=2, num_attention_heads=4, intermediate_size=128, max_position_embeddings=64,
+           hidden_dropout_prob=0.0, attention_probs_dropout_prob=0.0)
+
+
+def _ref_bert():
+    if not os.path.isdir(os.path.join(REF, "hetseq")):
+        pytest.skip("reference mount not present")
+    for stub in ("h5py", "boto3", "botocore", "botocore.exceptions"):
+        if stub not in sys.modules:
+            m = types.ModuleType(stub)
+            if stub == "botocore.exceptions":
+                m.ClientError = type("ClientError", (Exception,), {})
+            sys.modules[stub] = m
+    if REF not in sys.path:
+        sys.path.append(REF)
+        sys.path.append(os.path.join(REF, "hetseq"))
+    try:
+        import hetseq.bert_modeling as rb
+        return rb
+    except Exception as e:
+        pytest.skip("reference bert_modeling not importable: %r" % (e,))
+
+
+def test_state_dict_keys_and_losses_match_reference():
+    from hetseq_9cme_b200 import bert_modeling as bm
+    rb = _ref_bert()
+    torch.manual_seed(0)
+    ours = bm.BertForPreTraining(bm.BertConfig(500, **CFG))
+    theirs = rb.BertForPreTraining(rb.BertConfig(500, **CFG))
+    assert list(ours.state_dict().keys()) == list(theirs.state_dict().keys())
+    for (k, a), (_, b) in zip(ours.state_dict().items(), theirs.state_dict().items()):
+        assert a.shape == b.shape, k
+    theirs.load_state_dict(ours.state_dict())
+    ours.eval(); theirs.eval()
+    B, L = 3, 32
+    ids = torch.randint(1, 500, (B, L)); tts = torch.randint(0, 2, (B, L))
+    mask = torch.ones(B, L, dtype=torch.long); mask[1, 20:] = 0
+    mlm = torch.full((B, L), -1); mlm[:, 3:9] = ids[:, 3:9]
+    nsp = torch.tensor([0, 1, 0])
+    assert ours(ids, tts, mask, mlm, nsp).item() == pytest.approx(theirs(ids, tts, mask, mlm, nsp).item(), rel=2e-5)
+    ours_tc = bm.BertForTokenClassification(bm.BertConfig(500, **CFG), 5)
+    theirs_tc = rb.BertForTokenClassification(rb.BertConfig(500, **CFG), 5)
+    assert list(ours_tc.state_dict().keys()) == list(theirs_tc.state_dict().keys())
+    theirs_tc.load_state_dict(ours_tc.state_dict()); ours_tc.eval(); theirs_tc.eval()
+    lab = torch.randint(0, 5, (B, L)); lab[:, 0] = -100
+    assert ours_tc(ids, tts, mask, lab).item() == pytest.approx(theirs_tc(ids, tts, mask, lab).item(), rel=2e-5)
+    for name in ("BertForMaskedLM", "BertForNextSentencePrediction", "BertForQuestionAnswering"):
+        a = getattr(bm, name)(bm.BertConfig(500, **CFG)); b = getattr(rb, name)(rb.BertConfig(500, **CFG))
+        assert list(a.state_dict().keys()) == list(b.state_dict().keys()), name
+    a = bm.BertForSequenceClassification(bm.BertConfig(500, **CFG), 3); b = rb.BertForSequenceClassification(rb.BertConfig(500, **CFG), 3)
+    assert list(a.state_dict().keys()) == list(b.state_dict().keys())
+    a = bm.BertForMultipleChoice(bm.BertConfig(500, **CFG), 4); b = rb.BertForMultipleChoice(rb.BertConfig(500, **CFG), 4)
+    assert list(a.state_dict().keys()) == list(b.state_dict().keys())
+
+
+def test_bert_config_json_roundtrip(tmp_path):
+    from hetseq_9cme_b200 import bert_modeling as bm
+    from hetseq_9cme_b200.data import synthetic
+    p = synthetic.write_bert_config(str(tmp_path / "c.json"), hidden_size=128, num_hidden_layers=3)
+    c = bm.BertConfig.from_json_file(p)
+    assert c.hidden_size == 128 and c.num_hidden_layers == 3 and c.vocab_size == 30522
+    assert bm.BertConfig.from_dict(c.to_dict()).to_json_string() == c.to_json_string()
+
+
+def test_shard_formats_and_dataset_contract(tmp_path):
+    from hetseq_9cme_b200.data import BertH5pyData, ConBertH5pyData, shard_io, synthetic
+    d = str(tmp_path)
+    synthetic.make_bert_shards(d, n_train_files=2, samples_per_file=10, seq_len=32, max_pred=5, vocab_size=2000, fmt="b2s", test_samples=4)
+    shards = [BertH5pyData(os.path.join(d, "train_shard_%d.b2s" % i)) for i in range(2)]
+    ds = ConBertH5pyData(shards)
+    assert len(ds) == 20 and ds.num_tokens(3) == 512 and list(ds.ordered_indices()) == list(range(20))
+    raw = shard_io.open_shard(os.path.join(d, "train_shard_1.b2s"))
+    ids, seg, mask, lab, nsl = ds[13]                                  # global 13 -> shard 1, row 3
+    assert torch.equal(ids, torch.from_numpy(np.asarray(raw["input_ids"][3]).astype(np.int64)))
+    assert ids.dtype == seg.dtype == mask.dtype == lab.dtype == nsl.dtype == torch.int64
+    pos = np.asarray(raw["masked_lm_positions"][3]); mids = np.asarray(raw["masked_lm_ids"][3])
+    k = int(np.argmax(pos == 0)) if (pos == 0).any() else len(pos)
+    want = torch.full((32,), -1, dtype=torch.int64); want[torch.from_numpy(pos[:k].astype(np.int64))] = torch.from_numpy(mids[:k].astype(np.int64))
+    assert torch.equal(lab, want)
+    batch = ds.fetch_batch([8, 9, 10, 11])                             # straddles the shard boundary
+    coll = ds.collater([ds[i] for i in (8, 9, 10, 11)])
+    for a, b in zip(batch, coll):
+        assert torch.equal(a, b)
+    assert ds.collater([]) is None
+    # hdf5 round trip through the built-in minimal reader/writer
+    synthetic.make_bert_shards(d + "/h5", n_train_files=1, samples_per_file=6, seq_len=32, max_pred=5, vocab_size=2000, fmt="hdf5", test_samples=2)
+    h = BertH5pyData(os.path.join(d, "h5", "train_shard_0.hdf5"))
+    b2 = synthetic.bert_shard_arrays(6, 32, 5, 2000, 0)
+    assert torch.equal(h[2][0], torch.from_numpy(b2["input_ids"][2].astype(np.int64)))
+
+
+def test_collators_pad_to_longest():
+    from hetseq_9cme_b200.data_collator import YD_DataCollatorForELClassification, YD_DataCollatorForTokenClassification
+    feats = [{"input_ids": [2, 5, 6, 3], "labels": [-100, 1, 0, -100], "token_type_ids": [0] * 4, "attention_mask": [1] * 4},
+             {"input_ids": torch.tensor([2, 7, 3]), "labels": torch.tensor([-100, 2, -100]), "token_type_ids": [0] * 3, "attention_mask": [1] * 3}]
+    out = YD_DataCollatorForTokenClassification(tokenizer=None)(feats)
+    assert out["input_ids"].tolist() == [[2, 5, 6, 3], [2, 7, 3, 0]] and out["labels"].tolist()[1] == [-100, 2, -100, -100]
+    assert out["attention_mask"].tolist()[1] == [1, 1, 1, 0] and out["input_ids"].dtype == torch.int64
+    for f in feats:
+        f["entity_labels"] = [0] * len(f["labels"])
+    out = YD_DataCollatorForELClassification(tokenizer=None, pad_to_multiple_of=8)(feats)
+    assert out["entity_labels"].shape == (2, 8) and out["entity_labels"][1, 3:].tolist() == [-100] * 5
+
+
+def test_ner_and_bert_cli_runs_on_cpu(tmp_path):
+    from hetseq_9cme_b200 import options, train
+    from hetseq_9cme_b200.data import synthetic
+    d = str(tmp_path)
+    paths = synthetic.make_conll(d, n_train=48, n_valid=8, n_test=8, vocab_words=60)
+    cfg = synthetic.write_bert_config(os.path.join(d, "c.json"), vocab_size=65, **CFG)
+    argv = ["--task", "BertForTokenClassification", "--optimizer", "adam", "--data", d, "--dict", paths["vocab"], "--config_file", cfg,
+            "--train_file", paths["train"], "--validation_file", paths["validation"], "--test_file", paths["test"],
+            "--cpu", "--max-sentences", "8", "--lr", "1e-3", "--valid-subset", "test", "--save-dir", d + "/ck", "--max-epoch", "2",
+            "--distributed-world-size", "1", "--num-workers", "0", "--log-format", "none", "--warmup-updates", "2", "--total-num-update", "100"]
+    c = train.main(options.parse_training_args(argv))
+    assert c.get_num_updates() == 12 and c.get_model().num_labels == 9
+    first = torch.load(d + "/ck/checkpoint1.pt", weights_only=False)
+    assert "tokenizer" not in vars(first["args"]) and "bert.encoder.layer.0.attention.self.query.weight" in first["model"]
+    # warm-start a fresh NER model from that checkpoint (the --hetseq_state_dict path)
+    c2 = train.main(options.parse_training_args(argv + ["--hetseq_state_dict", d + "/ck/checkpoint1.pt", "--save-dir", d + "/ck2", "--max-epoch", "1"]))
+    assert c2.get_num_updates() == 6
+    # BERT pre-training, seq 32
+    synthetic.make_bert_shards(d + "/pt", n_train_files=2, samples_per_file=16, seq_len=32, max_pred=5, vocab_size=65, test_samples=8)
+    synthetic.write_vocab(d + "/v.txt", 65)
+    argv = ["--task", "bert", "--data", d + "/pt", "--dict", d + "/v.txt", "--config_file", cfg, "--cpu", "--max-sentences", "8",
+            "--lr", "1e-3", "--valid-subset", "test", "--save-dir", d + "/ck3", "--max-epoch", "2", "--distributed-world-size", "1",
+            "--num-workers", "0", "--log-format", "none", "--update-freq", "2", "--fast-stat-sync"]
+    c3 = train.main(options.parse_training_args(argv))
+    assert c3.get_num_updates() == 4 and os.path.exists(d + "/ck3/checkpoint_best.pt")

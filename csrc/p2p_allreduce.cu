@@ -1,0 +1,226 @@
+// p2p_allreduce.cu — gradient-bucket all-reduce over NVLink peer memory, written for the 8-GPU NVSwitch domain.
+//
+// Replaces DDP's Reducer + ncclAllReduce on the hot path (hetseq/controller.py:79-87).  Every rank maps every
+// peer's gradient arena and flag array (CUDA IPC, set up by ipc_export/ipc_open below) and runs ONE kernel per
+// bucket that
+//   1. announces "my bucket is final" to every peer (st.release.sys into the peer's flag array),
+//   2. waits until every peer has announced the same (ld.acquire.sys on its own, local flag array),
+//   3. two-shot: sums its 1/W slice of the bucket over all ranks in fixed rank order (bit-identical result on
+//      every rank) reading the peers' slices over NVLink, and writes the sum into every rank's arena
+//      (reduce-scatter by peer loads + all-gather by peer stores: 2(W-1)/W * S bytes per direction per GPU);
+//      one-shot for small buckets: every rank reads every peer's whole bucket and keeps the sum locally
+//      ((W-1) * S inbound, one barrier less);
+//   4. signals completion and waits for the peers' completion, so that when the kernel retires the local arena
+//      holds the fully reduced bucket and no peer is still reading it.
+// No host involvement after set-up; a dead peer turns into a trap after a bounded spin instead of a hang.
+#include <cuda.h>
+#include "common.h"
+#include "../include/b200seq.h"
+
+#include <cstring>
+
+namespace b200 {
+
+constexpr int kMaxRanks = 8;
+constexpr int kP2PThreads = 512;
+
+struct P2PArgs {
+  float* data[kMaxRanks];          // peers' arena base pointers (data[rank] is local)
+  unsigned int* flags[kMaxRanks];  // peers' flag arrays
+  unsigned int* counter;           // local: per-bucket block-arrival counters
+  int rank, world;
+  long long start, n;              // element range of the bucket inside the arena
+  int bucket;                      // flag slot
+  int max_buckets;
+  unsigned int epoch;
+  int one_shot;
+};
+
+__device__ __forceinline__ void st_release_sys(unsigned int* p, unsigned int v) {
+  asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ unsigned int ld_acquire_sys(const unsigned int* p) {
+  unsigned int v;
+  asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ float4 ld_peer_f4(const float* p) {
+  float4 v;
+  asm volatile("ld.volatile.global.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ void st_peer_f4(float* p, const float4& v) {
+  asm volatile("st.global.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(p), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w) : "memory");
+}
+
+__device__ __forceinline__ void wait_flag(const unsigned int* p, unsigned int epoch) {
+  long long t0 = clock64();
+  // epochs only grow; (int) difference handles wrap-around
+  while ((int)(ld_acquire_sys(p) - epoch) < 0) {
+    if (clock64() - t0 > 20000000000ll) {   // ~10 s
+      printf("b200seq p2p: peer flag wait timed out (block %d, want epoch %u, have %u)\n", blockIdx.x, epoch, *p);
+      __trap();
+    }
+    __nanosleep(64);
+  }
+}
+
+__device__ __forceinline__ int flag_index(int phase, int bucket, int src, int max_buckets) {
+  return (phase * max_buckets + bucket) * kMaxRanks + src;
+}
+
+__global__ void __launch_bounds__(kP2PThreads)
+p2p_allreduce_kernel(const P2PArgs a) {
+  const int t = threadIdx.x;
+  // ---- 1. announce, 2. wait for everyone's announcement --------------------------------------------------
+  if (blockIdx.x == 0 && t < a.world && t != a.rank) {
+    __threadfence_system();
+    st_release_sys(a.flags[t] + flag_index(0, a.bucket, a.rank, a.max_buckets), a.epoch);
+  }
+  if (t < a.world && t != a.rank) wait_flag(a.flags[a.rank] + flag_index(0, a.bucket, t, a.max_buckets), a.epoch);
+  __syncthreads();
+
+  const long long n4 = a.n >> 2;   // bucket ranges are multiples of 64 elements (arena alignment)
+  __shared__ bool last;
+
+  if (a.one_shot) {
+    // ---- one-shot (small buckets; host guarantees n4 <= gridDim.x * blockDim.x) ---------------------------
+    // Every rank reads every peer's bucket, keeps the sum in registers, and may overwrite its own copy only
+    // after ALL ranks have finished reading (second flag phase).
+    const long long i = (long long)blockIdx.x * blockDim.x + t;
+    const long long e = a.start + (i << 2);
+    float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (i < n4) {
+#pragma unroll
+      for (int p = 0; p < kMaxRanks; ++p) {
+        if (p < a.world) {
+          const float4 v = (p == a.rank) ? *reinterpret_cast<const float4*>(a.data[p] + e) : ld_peer_f4(a.data[p] + e);
+          acc.x += v.x; acc.y += v.y; acc.z += v.z; acc.w += v.w;
+        }
+      }
+    }
+    __syncthreads();
+    if (t == 0) {
+      const unsigned int prev = atomicAdd(a.counter + a.bucket, 1u);
+      last = (prev == gridDim.x - 1);
+    }
+    __syncthreads();
+    if (last) {
+      if (t == 0) a.counter[a.bucket] = 0;
+      if (t < a.world && t != a.rank) st_release_sys(a.flags[t] + flag_index(1, a.bucket, a.rank, a.max_buckets), a.epoch);
+    }
+    if (t < a.world && t != a.rank) wait_flag(a.flags[a.rank] + flag_index(1, a.bucket, t, a.max_buckets), a.epoch);
+    __syncthreads();
+    if (i < n4) *reinterpret_cast<float4*>(a.data[a.rank] + e) = acc;
+    return;
+  }
+
+  // ---- two-shot: reduce my slice over all ranks, push the result to every rank -----------------------------
+  {
+    const long long per = ((n4 + a.world - 1) / a.world);
+    const long long lo = per * a.rank, hi = (lo + per < n4) ? lo + per : n4;
+    for (long long i = lo + (long long)blockIdx.x * blockDim.x + t; i < hi; i += (long long)gridDim.x * blockDim.x) {
+      const long long e = a.start + (i << 2);
+      float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+      for (int p = 0; p < kMaxRanks; ++p) {
+        if (p < a.world) {
+          const float4 v = (p == a.rank) ? *reinterpret_cast<const float4*>(a.data[p] + e) : ld_peer_f4(a.data[p] + e);
+          acc.x += v.x; acc.y += v.y; acc.z += v.z; acc.w += v.w;
+        }
+      }
+#pragma unroll
+      for (int p = 0; p < kMaxRanks; ++p)
+        if (p < a.world) st_peer_f4(a.data[p] + e, acc);
+    }
+  }
+
+  // ---- completion: when the kernel retires, every peer has finished reading from and writing to this rank ----
+  __threadfence_system();
+  __syncthreads();
+  if (t == 0) {
+    const unsigned int prev = atomicAdd(a.counter + a.bucket, 1u);
+    last = (prev == gridDim.x - 1);
+  }
+  __syncthreads();
+  if (!last) return;
+  if (t == 0) a.counter[a.bucket] = 0;
+  if (t < a.world && t != a.rank) {
+    __threadfence_system();
+    st_release_sys(a.flags[t] + flag_index(1, a.bucket, a.rank, a.max_buckets), a.epoch);
+    wait_flag(a.flags[a.rank] + flag_index(1, a.bucket, t, a.max_buckets), a.epoch);
+  }
+}
+
+}  // namespace b200
+
+using namespace b200;
+
+// ---- CUDA IPC plumbing (host) -------------------------------------------------------------------------------
+// export: 64-byte handle of the allocation that contains `ptr` + the byte offset of `ptr` inside it
+extern "C" int b200_ipc_export(const void* ptr, unsigned char* handle_out /*64*/, long long* offset_out) {
+  if (!ptr || !handle_out || !offset_out) return fail(B200_ERR_ARG, "ipc_export: null pointer");
+  cudaIpcMemHandle_t h;
+  B200_CUDA(cudaIpcGetMemHandle(&h, const_cast<void*>(ptr)));
+  // the handle names the whole allocation; find its base to compute the offset
+  typedef CUresult (*GetRangeFn)(CUdeviceptr*, size_t*, CUdeviceptr);
+  static GetRangeFn get_range = nullptr;
+  if (!get_range) {
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuMemGetAddressRange", &p, cudaEnableDefault, &q) != cudaSuccess || !p)
+      return fail(B200_ERR_DRIVER, "ipc_export: cuMemGetAddressRange unavailable");
+    get_range = reinterpret_cast<GetRangeFn>(p);
+  }
+  CUdeviceptr base = 0;
+  size_t size = 0;
+  if (get_range(&base, &size, reinterpret_cast<CUdeviceptr>(ptr)) != CUDA_SUCCESS)
+    return fail(B200_ERR_DRIVER, "ipc_export: cuMemGetAddressRange failed");
+  static_assert(sizeof(cudaIpcMemHandle_t) == 64, "handle size");
+  std::memcpy(handle_out, &h, 64);
+  *offset_out = (long long)(reinterpret_cast<CUdeviceptr>(ptr) - base);
+  return 0;
+}
+
+extern "C" int b200_ipc_open(const unsigned char* handle /*64*/, long long offset, void** ptr_out, void** base_out) {
+  if (!handle || !ptr_out) return fail(B200_ERR_ARG, "ipc_open: null pointer");
+  cudaIpcMemHandle_t h;
+  std::memcpy(&h, handle, 64);
+  void* base = nullptr;
+  B200_CUDA(cudaIpcOpenMemHandle(&base, h, cudaIpcMemLazyEnablePeerAccess));
+  *ptr_out = static_cast<char*>(base) + offset;
+  if (base_out) *base_out = base;
+  return 0;
+}
+
+extern "C" int b200_ipc_close(void* base) {
+  if (!base) return 0;
+  B200_CUDA(cudaIpcCloseMemHandle(base));
+  return 0;
+}
+
+extern "C" int b200_p2p_allreduce(void* const* data_ptrs, void* const* flag_ptrs, void* counter, int rank, int world,
+                                  long long start, long long n, int bucket, int max_buckets, unsigned int epoch,
+                                  int one_shot, int blocks, void* stream) {
+  if (!data_ptrs || !flag_ptrs || !counter) return fail(B200_ERR_ARG, "p2p_allreduce: null pointer");
+  if (world < 2 || world > kMaxRanks || rank < 0 || rank >= world) return fail(B200_ERR_ARG, "p2p_allreduce: bad rank/world %d/%d", rank, world);
+  if ((start & 3) || (n & 3)) return fail(B200_ERR_ARG, "p2p_allreduce: range must be a multiple of 4 elements");
+  if (bucket < 0 || bucket >= max_buckets) return fail(B200_ERR_ARG, "p2p_allreduce: bucket index out of range");
+  P2PArgs a;
+  for (int i = 0; i < kMaxRanks; ++i) {
+    a.data[i] = i < world ? static_cast<float*>(data_ptrs[i]) : nullptr;
+    a.flags[i] = i < world ? static_cast<unsigned int*>(flag_ptrs[i]) : nullptr;
+  }
+  a.counter = static_cast<unsigned int*>(counter);
+  a.rank = rank; a.world = world; a.start = start; a.n = n; a.bucket = bucket; a.max_buckets = max_buckets;
+  a.epoch = epoch; a.one_shot = one_shot;
+  if (blocks <= 0) blocks = 32;
+  if (one_shot) {
+    const long long need = ((n >> 2) + kP2PThreads - 1) / kP2PThreads;
+    if (need > 4 * num_sms()) return fail(B200_ERR_ARG, "p2p_allreduce: bucket too large for one-shot mode");
+    blocks = (int)(need > 0 ? need : 1);
+  }
+  p2p_allreduce_kernel<<<blocks, kP2PThreads, 0, (cudaStream_t)stream>>>(a);
+  B200_LAUNCHED("p2p_allreduce_kernel");
+  return 0;
+}

@@ -1,0 +1,124 @@
+"""NVLink peer-to-peer gradient reducer (sm_100a kernels in ``csrc/p2p_allreduce.cu``).
+
+Set-up (once): every rank exports CUDA-IPC handles of its gradient arena and of a small flag array, the handles
+are exchanged through ``torch.distributed`` (control plane only), and every rank maps all peers' buffers.  After
+that a bucket reduction is ONE kernel launch per rank on a side stream — no NCCL, no host synchronisation, no
+copy-in/copy-out (the bucket *is* a slice of the arena the backward kernels wrote into).
+
+Replaces the DDP Reducer + ``ncclAllReduce`` of the reference (hetseq/controller.py:75-90).  Single NVSwitch
+domain only (<= 8 ranks on one node); anything else falls back to ``TorchReducer`` (see ``build_reducer``).
+"""
+from __future__ import annotations
+
+import ctypes
+from typing import List
+
+import torch
+import torch.distributed as dist
+
+from ..ops import native
+from .reducer import BaseReducer
+
+MAX_BUCKETS = 512
+MAX_RANKS = 8
+ONE_SHOT_BYTES = 256 * 1024
+
+
+def _declare(lib):
+    P, LL, I, U = ctypes.c_void_p, ctypes.c_longlong, ctypes.c_int, ctypes.c_uint
+    lib.b200_ipc_export.argtypes = [P, ctypes.c_char_p, ctypes.POINTER(LL)]
+    lib.b200_ipc_export.restype = I
+    lib.b200_ipc_open.argtypes = [ctypes.c_char_p, LL, ctypes.POINTER(P), ctypes.POINTER(P)]
+    lib.b200_ipc_open.restype = I
+    lib.b200_ipc_close.argtypes = [P]
+    lib.b200_ipc_close.restype = I
+    lib.b200_p2p_allreduce.argtypes = [ctypes.POINTER(P), ctypes.POINTER(P), P, I, I, LL, LL, I, I, U, I, I, P]
+    lib.b200_p2p_allreduce.restype = I
+
+
+class P2PReducer(BaseReducer):
+    def __init__(self, arena, world_size: int, blocks: int = 32):
+        super().__init__(arena, world_size)
+        if arena.device.type != "cuda":
+            raise RuntimeError("P2PReducer needs CUDA")
+        if world_size > MAX_RANKS:
+            raise RuntimeError("P2PReducer supports at most %d ranks (one NVSwitch domain)" % MAX_RANKS)
+        if len(arena.buckets) > MAX_BUCKETS:
+            raise RuntimeError("too many buckets for the flag array")
+        self.lib = native.cuda_lib()
+        _declare(self.lib)
+        self.rank = dist.get_rank()
+        self.blocks = blocks
+        dev = arena.device
+        self.flags = torch.zeros(2 * MAX_BUCKETS * MAX_RANKS, dtype=torch.int32, device=dev)
+        self.counter = torch.zeros(MAX_BUCKETS, dtype=torch.int32, device=dev)
+        torch.cuda.synchronize(dev)
+
+        def export(t: torch.Tensor):
+            buf = ctypes.create_string_buffer(64)
+            off = ctypes.c_longlong(0)
+            native.check(self.lib.b200_ipc_export(t.data_ptr(), buf, ctypes.byref(off)), "b200_ipc_export")
+            return bytes(buf.raw), int(off.value)
+
+        mine = {"rank": self.rank, "grad": export(arena.grad), "flags": export(self.flags), "numel": arena.numel,
+                "host": _hostname()}
+        gathered: List[dict] = [None] * world_size
+        dist.all_gather_object(gathered, mine)
+        if any(g["numel"] != arena.numel for g in gathered):
+            raise RuntimeError("ranks disagree on the arena layout")
+        if any(g["host"] != mine["host"] for g in gathered):
+            raise RuntimeError("ranks span several hosts: peer memory is unavailable")
+        self._opened = []
+        data_ptrs = (ctypes.c_void_p * MAX_RANKS)()
+        flag_ptrs = (ctypes.c_void_p * MAX_RANKS)()
+        for g in gathered:
+            r = g["rank"]
+            if r == self.rank:
+                data_ptrs[r] = arena.grad.data_ptr()
+                flag_ptrs[r] = self.flags.data_ptr()
+                continue
+            for key, arr in (("grad", data_ptrs), ("flags", flag_ptrs)):
+                handle, off = g[key]
+                p, base = ctypes.c_void_p(), ctypes.c_void_p()
+                native.check(self.lib.b200_ipc_open(handle, off, ctypes.byref(p), ctypes.byref(base)), "b200_ipc_open")
+                arr[r] = p.value
+                self._opened.append(base.value)
+        self.data_ptrs, self.flag_ptrs = data_ptrs, flag_ptrs
+        self.epoch = 0
+        self._side = torch.cuda.Stream(device=dev)
+        dist.barrier()
+
+    def begin(self, sync_now: bool):
+        super().begin(sync_now)
+        if self._active:
+            self.epoch += 1
+
+    def _launch(self, bi: int):
+        self._launched.add(bi)
+        s, e, _ = self.arena.buckets[bi]
+        n = e - s
+        ev = torch.cuda.Event()
+        ev.record(torch.cuda.current_stream())
+        self._side.wait_event(ev)
+        one_shot = 1 if n * 4 <= ONE_SHOT_BYTES else 0
+        native.check(self.lib.b200_p2p_allreduce(self.data_ptrs, self.flag_ptrs, self.counter.data_ptr(), self.rank,
+                                                 self.world_size, s, n, bi, MAX_BUCKETS, self.epoch & 0xFFFFFFFF, one_shot,
+                                                 self.blocks, self._side.cuda_stream), "b200_p2p_allreduce")
+
+    def _wait_all(self):
+        torch.cuda.current_stream().wait_stream(self._side)
+
+    def all_reduce_flat(self):
+        """Reduce the whole arena now (used by tests / when nothing was announced)."""
+        self.begin(True)
+        self.finish()
+
+    def close(self):
+        for base in self._opened:
+            self.lib.b200_ipc_close(base)
+        self._opened = []
+
+
+def _hostname() -> str:
+    import socket
+    return socket.gethostname()

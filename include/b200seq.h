@@ -196,6 +196,23 @@ int b200_softmax_fwd(int dtype, void* S, void* Pdrop, const long long* attn_mask
 int b200_softmax_bwd(int dtype, const void* P, void* dP, int B, int heads, int L, int Lp, float p_drop,
                      const unsigned long long* seed_dev, unsigned long long stream_id, void* stream);
 
+/* ------------------------------------------------------------------------------------------------
+ * Peer-to-peer gradient all-reduce over NVLink (replaces DDP's Reducer + ncclAllReduce,
+ * ref: hetseq/controller.py:79-87) and the CUDA-IPC plumbing that maps the peers' arenas.
+ * ---------------------------------------------------------------------------------------------- */
+int b200_ipc_export(const void* ptr, unsigned char* handle_out /* 64 bytes */, long long* offset_out);
+int b200_ipc_open(const unsigned char* handle /* 64 bytes */, long long offset, void** ptr_out, void** base_out);
+int b200_ipc_close(void* base);
+/* data_ptrs[r] / flag_ptrs[r]: rank r's gradient arena / flag array as mapped in THIS process (own rank = local
+ * pointer).  Flag arrays hold 2 * max_buckets * 8 uint32, zero-initialised; `counter` holds max_buckets uint32,
+ * zero-initialised, local.  `epoch` must increase by one per reduction of a given bucket, identically on all
+ * ranks.  SUM over ranks of arena[start, start+n) ends up in every rank's arena; one_shot=1 (small buckets) reads
+ * whole peer buckets, one_shot=0 is reduce-scatter + all-gather.  The kernel spins on peer flags: all ranks must
+ * launch it, each on its own GPU. */
+int b200_p2p_allreduce(void* const* data_ptrs, void* const* flag_ptrs, void* counter, int rank, int world,
+                       long long start, long long n, int bucket, int max_buckets, unsigned int epoch, int one_shot,
+                       int blocks, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -185,8 +185,10 @@ def run_ours(a):
         sync_all()
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record()
+        th0 = time.perf_counter()
         for s in range(a.steps):
             controller.train_step([staged[s % len(staged)]])
+        host_issue_ms = (time.perf_counter() - th0) * 1e3     # time the host needed to ISSUE the steps
         e1.record()
         sync_all()
         dev_ms = e0.elapsed_time(e1)
@@ -228,6 +230,7 @@ def run_ours(a):
                        "timing": "CUDA events on the training stream, max over ranks", "comm": type(controller.reducer).__name__,
                        "baseline_ref": "12.3 seq/s/GPU published (reference README.md:65, Pascal-era GPUs)"},
             "clocks": clocks, "gpu_launches": int(launches), "final_loss": round(float(loss_dev), 4),
+            "host_issue_ms_per_step": round(host_issue_ms / a.steps, 3),
         }
         if not a.no_e2e:
             out["e2e"] = {"value": round(gb * a.steps / (e2e_ms / 1e3), 2), "unit": "sequences/s",

@@ -410,21 +410,39 @@ head_bwd_dw_kernel(const float* __restrict__ dl, const T* __restrict__ x, long l
   }
 }
 
-// column sums: out[c] += sum_r x[r,c]   (bias gradients of the big GEMMs); two-stage through scratch
+// column sums: out[c] += sum_r x[r,c]   (bias gradients of the big GEMMs); two-stage through scratch.
+// Block (bx, by): 128 columns [bx*128, +128) x row range by; 8 warps interleave the rows (each warp reads a
+// coalesced 512 B row segment), partials meet in shared memory, scratch[by][c] gets the block's sum.
 template <typename T>
 __global__ void __launch_bounds__(256)
 colsum_partial_kernel(const T* __restrict__ x, long long ldx, int rows, int cols, int rows_per_block, float* __restrict__ scratch) {
-  // block (bx, by): columns [bx*1024, +1024), rows [by*rows_per_block, ...); thread owns 4 columns
-  const int c = blockIdx.x * 1024 + threadIdx.x * 4;
-  if (c >= cols) return;
+  __shared__ float4 red[8][32];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int c = blockIdx.x * 128 + lane * 4;
   const int r0 = blockIdx.y * rows_per_block;
   const int r1 = min(rows, r0 + rows_per_block);
   f4 acc = {0.f, 0.f, 0.f, 0.f};
-  for (int r = r0; r < r1; ++r) {
-    const f4 v = load4<T>(x + (long long)r * ldx + c);
-    acc.x += v.x; acc.y += v.y; acc.z += v.z; acc.w += v.w;
+  if (c < cols) {
+    int r = r0 + warp;
+    for (; r + 24 < r1; r += 32) {          // 4 independent loads in flight
+      const f4 v0 = load4<T>(x + (long long)r * ldx + c), v1 = load4<T>(x + (long long)(r + 8) * ldx + c);
+      const f4 v2 = load4<T>(x + (long long)(r + 16) * ldx + c), v3 = load4<T>(x + (long long)(r + 24) * ldx + c);
+      acc.x += (v0.x + v1.x) + (v2.x + v3.x); acc.y += (v0.y + v1.y) + (v2.y + v3.y);
+      acc.z += (v0.z + v1.z) + (v2.z + v3.z); acc.w += (v0.w + v1.w) + (v2.w + v3.w);
+    }
+    for (; r < r1; r += 8) {
+      const f4 v = load4<T>(x + (long long)r * ldx + c);
+      acc.x += v.x; acc.y += v.y; acc.z += v.z; acc.w += v.w;
+    }
   }
-  *reinterpret_cast<float4*>(scratch + (long long)blockIdx.y * cols + c) = make_float4(acc.x, acc.y, acc.z, acc.w);
+  red[warp][lane] = make_float4(acc.x, acc.y, acc.z, acc.w);
+  __syncthreads();
+  if (warp == 0 && c < cols) {
+    float4 t = red[0][lane];
+#pragma unroll
+    for (int w = 1; w < 8; ++w) { t.x += red[w][lane].x; t.y += red[w][lane].y; t.z += red[w][lane].z; t.w += red[w][lane].w; }
+    *reinterpret_cast<float4*>(scratch + (long long)blockIdx.y * cols + c) = t;
+  }
 }
 __global__ void __launch_bounds__(256)
 colsum_final_kernel(const float* __restrict__ scratch, int nparts, int cols, float* __restrict__ out) {
@@ -617,7 +635,7 @@ extern "C" int b200_colsum(int dtype, const void* x, long long ldx, int rows, in
   const int parts = rows >= 2048 ? 64 : (rows >= 256 ? 16 : 1);
   if (scratch_bytes < (long long)parts * cols * 4) return fail(B200_ERR_ARG, "colsum: scratch too small");
   const int rpb = (rows + parts - 1) / parts;
-  dim3 grid((cols + 1023) / 1024, parts);
+  dim3 grid((cols + 127) / 128, parts);
   DISPATCH_T(dtype, (colsum_partial_kernel<T><<<grid, 256, 0, (cudaStream_t)stream>>>((const T*)x, ldx, rows, cols, rpb, (float*)scratch)));
   B200_LAUNCHED("colsum_partial_kernel");
   colsum_final_kernel<<<(cols + 255) / 256, 256, 0, (cudaStream_t)stream>>>((const float*)scratch, parts, cols, out);
@@ -715,7 +733,7 @@ extern "C" int b200_colsum_static(int dtype, const void* x, long long ldx, int r
   if (rc) return rc;
   const int parts = rows >= 2048 ? kStaticColsumParts : (rows >= 256 ? 16 : 1);
   const int rpb = (rows + parts - 1) / parts;
-  dim3 grid((cols + 1023) / 1024, parts);
+  dim3 grid((cols + 127) / 128, parts);
   DISPATCH_T(dtype, (colsum_partial_kernel<T><<<grid, 256, 0, (cudaStream_t)stream>>>((const T*)x, ldx, rows, cols, rpb, scratch)));
   B200_LAUNCHED("colsum_partial_kernel(static)");
   colsum_final_kernel<<<(cols + 255) / 256, 256, 0, (cudaStream_t)stream>>>(scratch, parts, cols, out);

@@ -62,7 +62,7 @@ template <typename TIn, typename TOut, int BN, bool A_MN, bool B_MN, int STAGES>
 __global__ void __launch_bounds__(kGemmThreads, 1)
 gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                     const __grid_constant__ CUtensorMap tmD, const __grid_constant__ CUtensorMap tmD2,
-                    const GemmArgs args) {
+                    const __grid_constant__ CUtensorMap tmAux, const GemmArgs args) {
   constexpr int ES = sizeof(TIn);
   constexpr int BK = 128 / ES;        // elements of K per stage (one 128 B swizzle span)
   constexpr int UK = 32 / ES;         // K per tcgen05.mma (8 tf32 / 16 bf16)
@@ -88,7 +88,8 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
   uint64_t* empty_bar = bars + STAGES;
   uint64_t* tmem_full = bars + 2 * STAGES;
   uint64_t* tmem_empty = bars + 2 * STAGES + 2;
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * STAGES + 4);
+  uint64_t* aux_bar = bars + 2 * STAGES + 4;                   // [4 epilogue warps][2 staging buffers]
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * STAGES + 12);
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
@@ -105,6 +106,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
       mbar_init(&tmem_full[a], 1);
       mbar_init(&tmem_empty[a], 4);
     }
+    for (int a = 0; a < 8; ++a) mbar_init(&aux_bar[a], 1);
     fence_barrier_init();
   }
   if (warp == 1) tmem_alloc<TMEM_COLS>(tmem_slot);
@@ -201,6 +203,16 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
     const TOut* bias = reinterpret_cast<const TOut*>(args.bias);
     const TOut* aux = reinterpret_cast<const TOut*>(args.aux);
     const bool vec_ok = (args.N % (16 / OS)) == 0;
+    // aux tiles (residual / pre-activation) are fetched by TMA into the staging buffer the result will leave
+    // from, one chunk ahead of the math; the row-owner then reads its 128 B row from swizzled smem.
+    const bool tma_aux = (args.aux_mode != B200_AUX_NONE) && !args.has_d2;
+    uint64_t* my_aux_bar = aux_bar + ew * 2;
+    auto issue_aux = [&](int nc_, int m0_, uint32_t ev_) {       // lane 0 only
+      tma_store_wait_read<0>();                                  // every earlier store has left its buffer
+      uint64_t* bar = &my_aux_bar[ev_ & 1];
+      mbar_arrive_expect_tx(bar, kStageBufBytes);
+      tma_load_4d(stg + (ev_ & 1) * kStageBufBytes, &tmAux, bar, nc_, m0_, 0, 0);
+    };
 
     for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++tcount) {
       const int split = tile % args.splits;
@@ -215,6 +227,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
       tcgen05_fence_after();
       const int row = m0 + q * 32 + lane;
       const bool add_bias = (bias != nullptr) && (split == 0);
+      if (tma_aux && lane == 0 && n0 < args.N && m0 + q * 32 < args.M) issue_aux(n0, m0 + q * 32, ev);
 
 #pragma unroll 1
       for (int c = 0; c < BN / CW; ++c) {
@@ -292,7 +305,26 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
           for (int j = 0; j < CW; ++j) v[j] = tanhf(v[j]);
         }
 
-        if (args.aux_mode != B200_AUX_NONE && row < args.M) {
+        if (tma_aux) {
+          mbar_wait(&my_aux_bar[ev & 1], (ev >> 1) & 1);
+          const uint8_t* rowp = stg + (ev & 1) * kStageBufBytes + lane * 128;
+#pragma unroll
+          for (int i = 0; i < 8; ++i) {
+            const uint4 u = *reinterpret_cast<const uint4*>(rowp + ((i ^ (lane & 7)) << 4));
+            const TOut* a = reinterpret_cast<const TOut*>(&u);
+#pragma unroll
+            for (int e = 0; e < 16 / OS; ++e) {
+              const float x = to_f<TOut>(a[e]);
+              const int j = i * (16 / OS) + e;
+              if (args.aux_mode == B200_AUX_ADD) v[j] += x;
+              else if (args.aux_mode == B200_AUX_MUL_DGELU) v[j] *= dgelu_f(x);
+              else v[j] *= (1.0f - x * x);
+            }
+          }
+          __syncwarp();                                           // everyone has consumed the aux tile
+          const int nc_next = nc + CW;
+          if (lane == 0 && c + 1 < BN / CW && nc_next < args.N) issue_aux(nc_next, m0 + q * 32, ev + 1);
+        } else if (args.aux_mode != B200_AUX_NONE && row < args.M) {
           const TOut* arow = aux + (long long)row * args.ldaux + nc;
 #pragma unroll
           for (int j = 0; j < CW; j += 16 / OS) {
@@ -389,9 +421,9 @@ constexpr int stages_for() {
 
 template <typename TIn, typename TOut, int BN, bool A_MN, bool B_MN>
 static int launch_gemm(const CUtensorMap& tA, const CUtensorMap& tB, const CUtensorMap& tD, const CUtensorMap& tD2,
-                       const GemmArgs& args, cudaStream_t stream) {
+                       const CUtensorMap& tX, const GemmArgs& args, cudaStream_t stream) {
   constexpr int STAGES = stages_for<BN>();
-  constexpr int smem = STAGES * (kBM * 128 + BN * 128) + kEpiBytes + 1024 /*align*/ + (2 * STAGES + 4) * 8 + 16;
+  constexpr int smem = STAGES * (kBM * 128 + BN * 128) + kEpiBytes + 1024 /*align*/ + (2 * STAGES + 12) * 8 + 16;
   auto kern = gemm_tcgen05_kernel<TIn, TOut, BN, A_MN, B_MN, STAGES>;
   static bool attr_set = false;
   if (!attr_set) {
@@ -400,28 +432,28 @@ static int launch_gemm(const CUtensorMap& tA, const CUtensorMap& tB, const CUten
   }
   const long long tiles = (long long)args.nbatch * args.num_m * args.num_n * args.splits;
   const int grid = tiles < num_sms() ? (int)tiles : num_sms();
-  kern<<<grid, kGemmThreads, smem, stream>>>(tA, tB, tD, tD2, args);
+  kern<<<grid, kGemmThreads, smem, stream>>>(tA, tB, tD, tD2, tX, args);
   B200_LAUNCHED("gemm_tcgen05_kernel");
   return 0;
 }
 
 template <typename TIn, typename TOut, int BN>
 static int dispatch_major(bool a_mn, bool b_mn, const CUtensorMap& tA, const CUtensorMap& tB, const CUtensorMap& tD,
-                          const CUtensorMap& tD2, const GemmArgs& args, cudaStream_t stream) {
-  if (!a_mn && !b_mn) return launch_gemm<TIn, TOut, BN, false, false>(tA, tB, tD, tD2, args, stream);
-  if (!a_mn && b_mn) return launch_gemm<TIn, TOut, BN, false, true>(tA, tB, tD, tD2, args, stream);
-  if (a_mn && b_mn) return launch_gemm<TIn, TOut, BN, true, true>(tA, tB, tD, tD2, args, stream);
-  return launch_gemm<TIn, TOut, BN, true, false>(tA, tB, tD, tD2, args, stream);
+                          const CUtensorMap& tD2, const CUtensorMap& tX, const GemmArgs& args, cudaStream_t stream) {
+  if (!a_mn && !b_mn) return launch_gemm<TIn, TOut, BN, false, false>(tA, tB, tD, tD2, tX, args, stream);
+  if (!a_mn && b_mn) return launch_gemm<TIn, TOut, BN, false, true>(tA, tB, tD, tD2, tX, args, stream);
+  if (a_mn && b_mn) return launch_gemm<TIn, TOut, BN, true, true>(tA, tB, tD, tD2, tX, args, stream);
+  return launch_gemm<TIn, TOut, BN, true, false>(tA, tB, tD, tD2, tX, args, stream);
 }
 
 template <typename TIn, typename TOut>
 static int dispatch_bn(int bn, bool a_mn, bool b_mn, const CUtensorMap& tA, const CUtensorMap& tB, const CUtensorMap& tD,
-                       const CUtensorMap& tD2, const GemmArgs& args, cudaStream_t stream) {
+                       const CUtensorMap& tD2, const CUtensorMap& tX, const GemmArgs& args, cudaStream_t stream) {
   switch (bn) {
-    case 64: return dispatch_major<TIn, TOut, 64>(a_mn, b_mn, tA, tB, tD, tD2, args, stream);
-    case 128: return dispatch_major<TIn, TOut, 128>(a_mn, b_mn, tA, tB, tD, tD2, args, stream);
-    case 192: return dispatch_major<TIn, TOut, 192>(a_mn, b_mn, tA, tB, tD, tD2, args, stream);
-    case 256: return dispatch_major<TIn, TOut, 256>(a_mn, b_mn, tA, tB, tD, tD2, args, stream);
+    case 64: return dispatch_major<TIn, TOut, 64>(a_mn, b_mn, tA, tB, tD, tD2, tX, args, stream);
+    case 128: return dispatch_major<TIn, TOut, 128>(a_mn, b_mn, tA, tB, tD, tD2, tX, args, stream);
+    case 192: return dispatch_major<TIn, TOut, 192>(a_mn, b_mn, tA, tB, tD, tD2, tX, args, stream);
+    case 256: return dispatch_major<TIn, TOut, 256>(a_mn, b_mn, tA, tB, tD, tD2, tX, args, stream);
   }
   return fail(B200_ERR_ARG, "unsupported BN %d", bn);
 }
@@ -511,6 +543,11 @@ static int gemm_impl(const b200_gemm_desc* d, cudaStream_t stream) {
   } else {
     tD2 = tD;
   }
+  CUtensorMap tX = tD;
+  if (d->aux) {
+    rc = make_tmap_4d(&tX, d->aux, os, out_bf16, d->M, d->N, d->ldaux, CW, 32, false, 1, 0, 1, 0);
+    if (rc) return rc;
+  }
 
   GemmArgs a;
   a.M = d->M; a.N = d->N; a.K = d->K;
@@ -531,9 +568,9 @@ static int gemm_impl(const b200_gemm_desc* d, cudaStream_t stream) {
   a.alpha = d->alpha;
 
   switch (d->dtype) {
-    case B200_F32_TF32: return dispatch_bn<float, float>(bn, d->a_mn, d->b_mn, tA, tB, tD, tD2, a, stream);
-    case B200_BF16: return dispatch_bn<__nv_bfloat16, __nv_bfloat16>(bn, d->a_mn, d->b_mn, tA, tB, tD, tD2, a, stream);
-    case B200_BF16_F32OUT: return dispatch_bn<__nv_bfloat16, float>(bn, d->a_mn, d->b_mn, tA, tB, tD, tD2, a, stream);
+    case B200_F32_TF32: return dispatch_bn<float, float>(bn, d->a_mn, d->b_mn, tA, tB, tD, tD2, tX, a, stream);
+    case B200_BF16: return dispatch_bn<__nv_bfloat16, __nv_bfloat16>(bn, d->a_mn, d->b_mn, tA, tB, tD, tD2, tX, a, stream);
+    case B200_BF16_F32OUT: return dispatch_bn<__nv_bfloat16, float>(bn, d->a_mn, d->b_mn, tA, tB, tD, tD2, tX, a, stream);
   }
   return fail(B200_ERR_ARG, "gemm: unknown dtype %d", d->dtype);
 }

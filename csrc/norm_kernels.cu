@@ -190,6 +190,113 @@ ln_bwd_kernel(const LnCommon<T> a, const T* __restrict__ dy, long long lddy, con
   }
 }
 
+
+// Two warps per row: halves the per-thread column accumulators (register pressure was capping the one-warp
+// version at one block per SM).  Block = 8 warps = 4 rows per iteration; row statistics are combined through
+// shared memory (double-buffered by iteration parity -> one __syncthreads per iteration).  cols % 256 == 0.
+template <typename T, int NVH>
+__global__ void __launch_bounds__(kLnThreads, 2)
+ln_bwd2_kernel(const LnCommon<T> a, const T* __restrict__ dy, long long lddy, const float* __restrict__ mean_in,
+               const float* __restrict__ rstd_in, T* __restrict__ ds, long long ldds, T* __restrict__ dz, long long lddz,
+               float* __restrict__ scratch, int want_dbias) {
+  extern __shared__ float red[];            // [4 row-slots][cols] for the final fold
+  __shared__ float2 part[2][4][2];          // [parity][row slot][half]
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int slot = warp >> 1, half = warp & 1;
+  const unsigned long long seed = a.seed_dev ? *a.seed_dev : 0ull;
+  const Philox ph(seed);
+  const uint32_t thr_pre = dropout_threshold(a.p_pre), thr_post = dropout_threshold(a.p_post);
+  const float ikp = a.p_pre > 0.f ? 1.f / (1.f - a.p_pre) : 1.f;
+  const float ikq = a.p_post > 0.f ? 1.f / (1.f - a.p_post) : 1.f;
+  const float inv_cols = 1.f / (float)a.cols;
+  const int cbase = half * (a.cols >> 1);
+  f4 acc_g[NVH], acc_b[NVH], acc_bias[NVH];
+#pragma unroll
+  for (int k = 0; k < NVH; ++k) acc_g[k] = acc_b[k] = acc_bias[k] = {0.f, 0.f, 0.f, 0.f};
+
+  int it = 0;
+  for (int base = blockIdx.x * 4; base < a.rows; base += gridDim.x * 4, ++it) {
+    const int row = base + slot;
+    const bool live = row < a.rows;
+    f4 v[NVH], g[NVH];
+    uint32_t mbits = 0xFFFFFFFFu;            // pre-dropout keep bits, 4 per vector
+    float s1 = 0.f, s2 = 0.f, mean = 0.f, rstd = 0.f;
+    if (live) {
+      mean = mean_in[row];
+      rstd = rstd_in[row];
+#pragma unroll
+      for (int k = 0; k < NVH; ++k) {
+        const int c = cbase + (k * 32 + lane) * 4;
+        f4 t = load4<T>(a.x + (long long)row * a.ldx + c);
+        if (a.bias) {
+          const f4 b = load4<T>(a.bias + c);
+          t.x += b.x; t.y += b.y; t.z += b.z; t.w += b.w;
+        }
+        if (a.p_pre > 0.f) {
+          const f4 m = dropout_scale4(ph, (unsigned long long)row * a.cols + c, a.stream_pre, thr_pre, ikp);
+          t.x *= m.x; t.y *= m.y; t.z *= m.z; t.w *= m.w;
+          const uint32_t bits = (m.x != 0.f ? 1u : 0u) | (m.y != 0.f ? 2u : 0u) | (m.z != 0.f ? 4u : 0u) | (m.w != 0.f ? 8u : 0u);
+          mbits = (mbits & ~(0xFu << (4 * k))) | (bits << (4 * k));
+        }
+        if (a.residual) {
+          const f4 r = load4<T>(a.residual + (long long)row * a.ldr + c);
+          t.x += r.x; t.y += r.y; t.z += r.z; t.w += r.w;
+        }
+        f4 d = load4<T>(dy + (long long)row * lddy + c);
+        if (a.p_post > 0.f) {
+          const f4 m = dropout_scale4(ph, (unsigned long long)row * a.cols + c, a.stream_post, thr_post, ikq);
+          d.x *= m.x; d.y *= m.y; d.z *= m.z; d.w *= m.w;
+        }
+        const f4 gm = load4<T>(a.gamma + c);
+        v[k] = {(t.x - mean) * rstd, (t.y - mean) * rstd, (t.z - mean) * rstd, (t.w - mean) * rstd};
+        acc_g[k].x += d.x * v[k].x; acc_g[k].y += d.y * v[k].y; acc_g[k].z += d.z * v[k].z; acc_g[k].w += d.w * v[k].w;
+        acc_b[k].x += d.x; acc_b[k].y += d.y; acc_b[k].z += d.z; acc_b[k].w += d.w;
+        g[k] = {d.x * gm.x, d.y * gm.y, d.z * gm.z, d.w * gm.w};
+        s1 += g[k].x + g[k].y + g[k].z + g[k].w;
+        s2 += g[k].x * v[k].x + g[k].y * v[k].y + g[k].z * v[k].z + g[k].w * v[k].w;
+      }
+    }
+    s1 = warp_sum(s1);
+    s2 = warp_sum(s2);
+    if (lane == 0) part[it & 1][slot][half] = make_float2(s1, s2);
+    __syncthreads();
+    if (live) {
+      const float2 p0 = part[it & 1][slot][0], p1 = part[it & 1][slot][1];
+      const float c1 = (p0.x + p1.x) * inv_cols, c2 = (p0.y + p1.y) * inv_cols;
+#pragma unroll
+      for (int k = 0; k < NVH; ++k) {
+        const int c = cbase + (k * 32 + lane) * 4;
+        f4 o = {rstd * (g[k].x - c1 - v[k].x * c2), rstd * (g[k].y - c1 - v[k].y * c2),
+                rstd * (g[k].z - c1 - v[k].z * c2), rstd * (g[k].w - c1 - v[k].w * c2)};
+        if (ds) store4<T>(ds + (long long)row * ldds + c, o);
+        if (a.p_pre > 0.f) {
+          const uint32_t b = (mbits >> (4 * k)) & 0xFu;
+          o.x = (b & 1u) ? o.x * ikp : 0.f; o.y = (b & 2u) ? o.y * ikp : 0.f;
+          o.z = (b & 4u) ? o.z * ikp : 0.f; o.w = (b & 8u) ? o.w * ikp : 0.f;
+        }
+        if (dz) store4<T>(dz + (long long)row * lddz + c, o);
+        acc_bias[k].x += o.x; acc_bias[k].y += o.y; acc_bias[k].z += o.z; acc_bias[k].w += o.w;
+      }
+    }
+  }
+
+  float* out = scratch + (long long)blockIdx.x * 3 * a.cols;
+#pragma unroll 1
+  for (int qn = 0; qn < 3; ++qn) {
+    if (qn == 2 && !want_dbias) break;
+    __syncthreads();
+#pragma unroll
+    for (int k = 0; k < NVH; ++k) {
+      const int c = cbase + (k * 32 + lane) * 4;
+      const f4 t = qn == 0 ? acc_g[k] : (qn == 1 ? acc_b[k] : acc_bias[k]);
+      *reinterpret_cast<float4*>(red + slot * a.cols + c) = make_float4(t.x, t.y, t.z, t.w);
+    }
+    __syncthreads();
+    for (int c = threadIdx.x; c < a.cols; c += kLnThreads)
+      out[qn * a.cols + c] = red[c] + red[a.cols + c] + red[2 * a.cols + c] + red[3 * a.cols + c];
+  }
+}
+
 // dgamma/dbeta/dbias[c] += sum_b scratch[b][q][c]; one block = 32 columns x 8 row-lanes
 __global__ void __launch_bounds__(256)
 ln_bwd_finalize(const float* __restrict__ scratch, int nblocks, int cols, float* __restrict__ dgamma,
@@ -257,6 +364,29 @@ static int ln_bwd_blocks(int rows) {
 template <typename T>
 static int ln_bwd_t(const b200_ln_args* a, cudaStream_t st) {
   const LnCommon<T> c = make_common<T>(a);
+  if ((a->cols & 255) == 0) {
+    // two warps per row
+    int blocks = (a->rows + 3) / 4;
+    if (blocks > kLnBwdMaxBlocks) blocks = kLnBwdMaxBlocks;
+    if (blocks < 1) blocks = 1;
+    const size_t smem2 = (size_t)4 * a->cols * sizeof(float);
+    const int want = a->dbias != nullptr;
+#define LN_BWD2(NVH)                                                                                                  \
+  ln_bwd2_kernel<T, NVH><<<blocks, kLnThreads, smem2, st>>>(c, (const T*)a->dy, a->lddy, a->mean, a->rstd, (T*)a->ds,  \
+                                                            a->ldds, (T*)a->dz, a->lddz, (float*)a->scratch, want)
+    switch (a->cols / 256) {
+      case 1: LN_BWD2(1); break;
+      case 2: LN_BWD2(2); break;
+      case 3: LN_BWD2(3); break;
+      default: LN_BWD2(4); break;
+    }
+#undef LN_BWD2
+    B200_LAUNCHED("ln_bwd2_kernel");
+    dim3 grid2((a->cols + 31) / 32, 3);
+    ln_bwd_finalize<<<grid2, 256, 0, st>>>((const float*)a->scratch, blocks, a->cols, a->dgamma, a->dbeta, a->dbias);
+    B200_LAUNCHED("ln_bwd_finalize");
+    return 0;
+  }
   const int blocks = ln_bwd_blocks(a->rows);
   const size_t smem = (size_t)kLnWarps * a->cols * sizeof(float);
   const int want_dbias = a->dbias != nullptr;

@@ -32,7 +32,7 @@ struct P2PArgs {
   long long start, n;              // element range of the bucket inside the arena
   int bucket;                      // flag slot
   int max_buckets;
-  unsigned int epoch;
+  unsigned int* epoch_dev;         // local: per-bucket epoch words (advanced by the kernel itself)
   int one_shot;
 };
 
@@ -72,12 +72,16 @@ __device__ __forceinline__ int flag_index(int phase, int bucket, int src, int ma
 __global__ void __launch_bounds__(kP2PThreads)
 p2p_allreduce_kernel(const P2PArgs a) {
   const int t = threadIdx.x;
+  // Every rank launches the same sequence of reductions, so a per-bucket counter kept on each device yields the
+  // same epoch everywhere without a host-supplied value (lets a captured CUDA graph be replayed).  It is advanced
+  // by the last block, after every block has read it.
+  const unsigned int epoch = a.epoch_dev[a.bucket] + 1u;
   // ---- 1. announce, 2. wait for everyone's announcement --------------------------------------------------
   if (blockIdx.x == 0 && t < a.world && t != a.rank) {
     __threadfence_system();
-    st_release_sys(a.flags[t] + flag_index(0, a.bucket, a.rank, a.max_buckets), a.epoch);
+    st_release_sys(a.flags[t] + flag_index(0, a.bucket, a.rank, a.max_buckets), epoch);
   }
-  if (t < a.world && t != a.rank) wait_flag(a.flags[a.rank] + flag_index(0, a.bucket, t, a.max_buckets), a.epoch);
+  if (t < a.world && t != a.rank) wait_flag(a.flags[a.rank] + flag_index(0, a.bucket, t, a.max_buckets), epoch);
   __syncthreads();
 
   const long long n4 = a.n >> 2;   // bucket ranges are multiples of 64 elements (arena alignment)
@@ -106,10 +110,10 @@ p2p_allreduce_kernel(const P2PArgs a) {
     }
     __syncthreads();
     if (last) {
-      if (t == 0) a.counter[a.bucket] = 0;
-      if (t < a.world && t != a.rank) st_release_sys(a.flags[t] + flag_index(1, a.bucket, a.rank, a.max_buckets), a.epoch);
+      if (t == 0) { a.counter[a.bucket] = 0; a.epoch_dev[a.bucket] = epoch; }
+      if (t < a.world && t != a.rank) st_release_sys(a.flags[t] + flag_index(1, a.bucket, a.rank, a.max_buckets), epoch);
     }
-    if (t < a.world && t != a.rank) wait_flag(a.flags[a.rank] + flag_index(1, a.bucket, t, a.max_buckets), a.epoch);
+    if (t < a.world && t != a.rank) wait_flag(a.flags[a.rank] + flag_index(1, a.bucket, t, a.max_buckets), epoch);
     __syncthreads();
     if (i < n4) *reinterpret_cast<float4*>(a.data[a.rank] + e) = acc;
     return;
@@ -119,19 +123,34 @@ p2p_allreduce_kernel(const P2PArgs a) {
   {
     const long long per = ((n4 + a.world - 1) / a.world);
     const long long lo = per * a.rank, hi = (lo + per < n4) ? lo + per : n4;
-    for (long long i = lo + (long long)blockIdx.x * blockDim.x + t; i < hi; i += (long long)gridDim.x * blockDim.x) {
-      const long long e = a.start + (i << 2);
-      float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+    const long long stride = (long long)gridDim.x * blockDim.x;
+    constexpr int U = 4;                      // independent 16-byte requests per peer in flight per thread
+    for (long long i0 = lo + (long long)blockIdx.x * blockDim.x + t; i0 < hi; i0 += U * stride) {
+      float4 v[U][kMaxRanks];
 #pragma unroll
-      for (int p = 0; p < kMaxRanks; ++p) {
-        if (p < a.world) {
-          const float4 v = (p == a.rank) ? *reinterpret_cast<const float4*>(a.data[p] + e) : ld_peer_f4(a.data[p] + e);
-          acc.x += v.x; acc.y += v.y; acc.z += v.z; acc.w += v.w;
+      for (int u = 0; u < U; ++u) {
+        const long long i = i0 + u * stride;
+        if (i < hi) {
+          const long long e = a.start + (i << 2);
+#pragma unroll
+          for (int p = 0; p < kMaxRanks; ++p)
+            if (p < a.world) v[u][p] = (p == a.rank) ? *reinterpret_cast<const float4*>(a.data[p] + e) : ld_peer_f4(a.data[p] + e);
         }
       }
 #pragma unroll
-      for (int p = 0; p < kMaxRanks; ++p)
-        if (p < a.world) st_peer_f4(a.data[p] + e, acc);
+      for (int u = 0; u < U; ++u) {
+        const long long i = i0 + u * stride;
+        if (i < hi) {
+          const long long e = a.start + (i << 2);
+          float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+          for (int p = 0; p < kMaxRanks; ++p)      // fixed rank order -> identical bits on every rank
+            if (p < a.world) { acc.x += v[u][p].x; acc.y += v[u][p].y; acc.z += v[u][p].z; acc.w += v[u][p].w; }
+#pragma unroll
+          for (int p = 0; p < kMaxRanks; ++p)
+            if (p < a.world) st_peer_f4(a.data[p] + e, acc);
+        }
+      }
     }
   }
 
@@ -144,11 +163,11 @@ p2p_allreduce_kernel(const P2PArgs a) {
   }
   __syncthreads();
   if (!last) return;
-  if (t == 0) a.counter[a.bucket] = 0;
+  if (t == 0) { a.counter[a.bucket] = 0; a.epoch_dev[a.bucket] = epoch; }
   if (t < a.world && t != a.rank) {
     __threadfence_system();
-    st_release_sys(a.flags[t] + flag_index(1, a.bucket, a.rank, a.max_buckets), a.epoch);
-    wait_flag(a.flags[a.rank] + flag_index(1, a.bucket, t, a.max_buckets), a.epoch);
+    st_release_sys(a.flags[t] + flag_index(1, a.bucket, a.rank, a.max_buckets), epoch);
+    wait_flag(a.flags[a.rank] + flag_index(1, a.bucket, t, a.max_buckets), epoch);
   }
 }
 
@@ -200,9 +219,9 @@ extern "C" int b200_ipc_close(void* base) {
 }
 
 extern "C" int b200_p2p_allreduce(void* const* data_ptrs, void* const* flag_ptrs, void* counter, int rank, int world,
-                                  long long start, long long n, int bucket, int max_buckets, unsigned int epoch,
+                                  long long start, long long n, int bucket, int max_buckets, void* epoch_dev,
                                   int one_shot, int blocks, void* stream) {
-  if (!data_ptrs || !flag_ptrs || !counter) return fail(B200_ERR_ARG, "p2p_allreduce: null pointer");
+  if (!data_ptrs || !flag_ptrs || !counter || !epoch_dev) return fail(B200_ERR_ARG, "p2p_allreduce: null pointer");
   if (world < 2 || world > kMaxRanks || rank < 0 || rank >= world) return fail(B200_ERR_ARG, "p2p_allreduce: bad rank/world %d/%d", rank, world);
   if ((start & 3) || (n & 3)) return fail(B200_ERR_ARG, "p2p_allreduce: range must be a multiple of 4 elements");
   if (bucket < 0 || bucket >= max_buckets) return fail(B200_ERR_ARG, "p2p_allreduce: bucket index out of range");
@@ -213,7 +232,7 @@ extern "C" int b200_p2p_allreduce(void* const* data_ptrs, void* const* flag_ptrs
   }
   a.counter = static_cast<unsigned int*>(counter);
   a.rank = rank; a.world = world; a.start = start; a.n = n; a.bucket = bucket; a.max_buckets = max_buckets;
-  a.epoch = epoch; a.one_shot = one_shot;
+  a.epoch_dev = static_cast<unsigned int*>(epoch_dev); a.one_shot = one_shot;
   if (blocks <= 0) blocks = 32;
   if (one_shot) {
     const long long need = ((n >> 2) + kP2PThreads - 1) / kP2PThreads;

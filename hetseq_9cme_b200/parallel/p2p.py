@@ -32,12 +32,12 @@ def _declare(lib):
     lib.b200_ipc_open.restype = I
     lib.b200_ipc_close.argtypes = [P]
     lib.b200_ipc_close.restype = I
-    lib.b200_p2p_allreduce.argtypes = [ctypes.POINTER(P), ctypes.POINTER(P), P, I, I, LL, LL, I, I, U, I, I, P]
+    lib.b200_p2p_allreduce.argtypes = [ctypes.POINTER(P), ctypes.POINTER(P), P, I, I, LL, LL, I, I, P, I, I, P]
     lib.b200_p2p_allreduce.restype = I
 
 
 class P2PReducer(BaseReducer):
-    def __init__(self, arena, world_size: int, blocks: int = 32):
+    def __init__(self, arena, world_size: int, blocks: int = 48):
         super().__init__(arena, world_size)
         if arena.device.type != "cuda":
             raise RuntimeError("P2PReducer needs CUDA")
@@ -52,6 +52,7 @@ class P2PReducer(BaseReducer):
         dev = arena.device
         self.flags = torch.zeros(2 * MAX_BUCKETS * MAX_RANKS, dtype=torch.int32, device=dev)
         self.counter = torch.zeros(MAX_BUCKETS, dtype=torch.int32, device=dev)
+        self.epochs = torch.zeros(MAX_BUCKETS, dtype=torch.int32, device=dev)
         torch.cuda.synchronize(dev)
 
         def export(t: torch.Tensor):
@@ -102,7 +103,7 @@ class P2PReducer(BaseReducer):
         self._side.wait_event(ev)
         one_shot = 1 if n * 4 <= ONE_SHOT_BYTES else 0
         native.check(self.lib.b200_p2p_allreduce(self.data_ptrs, self.flag_ptrs, self.counter.data_ptr(), self.rank,
-                                                 self.world_size, s, n, bi, MAX_BUCKETS, self.epoch & 0xFFFFFFFF, one_shot,
+                                                 self.world_size, s, n, bi, MAX_BUCKETS, self.epochs.data_ptr(), one_shot,
                                                  self.blocks, self._side.cuda_stream), "b200_p2p_allreduce")
 
     def _wait_all(self):

@@ -205,12 +205,12 @@ int b200_ipc_open(const unsigned char* handle /* 64 bytes */, long long offset, 
 int b200_ipc_close(void* base);
 /* data_ptrs[r] / flag_ptrs[r]: rank r's gradient arena / flag array as mapped in THIS process (own rank = local
  * pointer).  Flag arrays hold 2 * max_buckets * 8 uint32, zero-initialised; `counter` holds max_buckets uint32,
- * zero-initialised, local.  `epoch` must increase by one per reduction of a given bucket, identically on all
- * ranks.  SUM over ranks of arena[start, start+n) ends up in every rank's arena; one_shot=1 (small buckets) reads
+ * zero-initialised, local.  `epoch_dev` holds max_buckets uint32 (zero-initialised, local): the kernel derives
+ * the flag epoch from it and advances it, so all ranks must issue the same sequence of reductions.  SUM over ranks of arena[start, start+n) ends up in every rank's arena; one_shot=1 (small buckets) reads
  * whole peer buckets, one_shot=0 is reduce-scatter + all-gather.  The kernel spins on peer flags: all ranks must
  * launch it, each on its own GPU. */
 int b200_p2p_allreduce(void* const* data_ptrs, void* const* flag_ptrs, void* counter, int rank, int world,
-                       long long start, long long n, int bucket, int max_buckets, unsigned int epoch, int one_shot,
+                       long long start, long long n, int bucket, int max_buckets, void* epoch_dev, int one_shot,
                        int blocks, void* stream);
 
 #ifdef __cplusplus

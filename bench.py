@@ -47,6 +47,7 @@ def parse():
     ap.add_argument("--model", default="bert-base", choices=["bert-base", "bert-large", "bert-tiny"])
     ap.add_argument("--comm", default="auto")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-graph", action="store_true", help="issue every kernel from Python instead of replaying a CUDA graph")
     return ap.parse_args()
 
 
@@ -122,6 +123,8 @@ def make_args(a, data_dir, cfg_path, vocab_path, rank, local, world):
             "--valid-subset", "test", "--num-workers", "2", "--save-dir", os.path.join(data_dir, "ckpt"), "--no-save",
             "--log-format", "none", "--distributed-world-size", str(world), "--precision", a.precision, "--comm", a.comm,
             "--max-predictions-per-seq", "20" if a.seq_len <= 128 else "80", "--disable-validation"]
+    if not a.no_graph:
+        argv.append("--cuda-graph")
     args = options.parse_training_args(argv)
     args.distributed_rank = rank
     args.device_id = local
@@ -228,6 +231,7 @@ def run_ours(a):
                        "parallelism": "dp%d" % world, "optimizer": "adam (fused, fp32 master)", "dropout": 0.1,
                        "max_predictions_per_seq": max_pred, "l2_policy": "per-step working set (>= 440 MB) exceeds the 126 MB L2",
                        "timing": "CUDA events on the training stream, max over ranks", "comm": type(controller.reducer).__name__,
+                       "cuda_graph": bool(controller._graph is not None),
                        "baseline_ref": "12.3 seq/s/GPU published (reference README.md:65, Pascal-era GPUs)"},
             "clocks": clocks, "gpu_launches": int(launches), "final_loss": round(float(loss_dev), 4),
             "host_issue_ms_per_step": round(host_issue_ms / a.steps, 3),

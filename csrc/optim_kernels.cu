@@ -82,13 +82,16 @@ struct StepScalars {
   float clipped; // 1 if the clip coefficient was applied
 };
 
-__device__ __forceinline__ StepScalars derive_scalars(float mult, const double* sample_size, const float* norm_sq,
-                                                      float max_norm) {
+__device__ __forceinline__ StepScalars derive_scalars(float mult, const double* sample_size, const float* sample_size_f32,
+                                                      const float* norm_sq, float max_norm) {
   StepScalars s;
   float c = mult;
   if (sample_size != nullptr) {
     const double ss = *sample_size;
     c = ss > 0.0 ? (float)((double)mult / ss) : 0.f;
+  } else if (sample_size_f32 != nullptr) {
+    const float ss = *sample_size_f32;
+    c = ss > 0.f ? mult / ss : 0.f;
   }
   s.scale = c;
   s.gnorm = 0.f;
@@ -112,19 +115,26 @@ struct AdamArgsDev {
   const double* sample_size;
   float* stats_out;
   int zero_grad;
+  const float* sample_size_f32;
+  const float* hyper_dev;   // optional device float[4]: lr, step_size, (1 - wd*lr), unused — overrides the by-value copies
 };
 
 __global__ void __launch_bounds__(256)
 adam_flat_kernel(float* __restrict__ p, float* __restrict__ g, float* __restrict__ m, float* __restrict__ v,
-                 __nv_bfloat16* __restrict__ p16, long long n, const AdamArgsDev a) {
-  const StepScalars sc = derive_scalars(a.mult, a.sample_size, a.norm_sq, a.max_norm);
+                 __nv_bfloat16* __restrict__ p16, long long n, AdamArgsDev a) {
+  float decay = 1.f - a.weight_decay * a.lr;
+  if (a.hyper_dev != nullptr) {            // values that change every step come from device memory (graph replay)
+    a.lr = a.hyper_dev[0];
+    a.step_size = a.hyper_dev[1];
+    decay = a.hyper_dev[2];
+  }
+  const StepScalars sc = derive_scalars(a.mult, a.sample_size, a.sample_size_f32, a.norm_sq, a.max_norm);
   if (blockIdx.x == 0 && threadIdx.x == 0 && a.stats_out != nullptr) {
     a.stats_out[0] = sc.gnorm;
     a.stats_out[1] = sc.scale;
     a.stats_out[2] = sc.clipped;
   }
   const float one_m_b1 = 1.f - a.beta1, one_m_b2 = 1.f - a.beta2;
-  const float decay = 1.f - a.weight_decay * a.lr;
   const long long n4 = n >> 2;
   for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += (long long)gridDim.x * blockDim.x) {
     float4 pv = reinterpret_cast<float4*>(p)[i];
@@ -169,13 +179,16 @@ struct AdadeltaArgsDev {
   const double* sample_size;
   float* stats_out;
   int zero_grad;
+  const float* sample_size_f32;
+  const float* hyper_dev;
 };
 
 // reference math: hetseq/optim.py:293-302
 __global__ void __launch_bounds__(256)
 adadelta_flat_kernel(float* __restrict__ p, float* __restrict__ g, float* __restrict__ sq, float* __restrict__ acc,
-                     __nv_bfloat16* __restrict__ p16, long long n, const AdadeltaArgsDev a) {
-  const StepScalars sc = derive_scalars(a.mult, a.sample_size, a.norm_sq, a.max_norm);
+                     __nv_bfloat16* __restrict__ p16, long long n, AdadeltaArgsDev a) {
+  if (a.hyper_dev != nullptr) a.lr = a.hyper_dev[0];
+  const StepScalars sc = derive_scalars(a.mult, a.sample_size, a.sample_size_f32, a.norm_sq, a.max_norm);
   if (blockIdx.x == 0 && threadIdx.x == 0 && a.stats_out != nullptr) {
     a.stats_out[0] = sc.gnorm;
     a.stats_out[1] = sc.scale;
@@ -252,6 +265,7 @@ extern "C" int b200_adam_flat(float* p, float* g, float* m, float* v, void* p_bf
   d.step_size = (float)((double)a->lr * sqrt(bc2) / bc1);
   d.mult = a->grad_scale_mult; d.max_norm = a->max_norm;
   d.norm_sq = a->norm_sq; d.sample_size = a->sample_size; d.stats_out = a->stats_out; d.zero_grad = a->zero_grad;
+  d.sample_size_f32 = a->sample_size_f32; d.hyper_dev = a->hyper_dev;
   adam_flat_kernel<<<elementwise_grid(n / 4 + 1, 256), 256, 0, (cudaStream_t)stream>>>(p, g, m, v, (__nv_bfloat16*)p_bf16, n, d);
   B200_LAUNCHED("adam_flat_kernel");
   return 0;
@@ -264,6 +278,7 @@ extern "C" int b200_adadelta_flat(float* p, float* g, float* sq, float* acc, voi
   d.lr = a->lr; d.rho = a->rho; d.eps = a->eps; d.weight_decay = a->weight_decay;
   d.mult = a->grad_scale_mult; d.max_norm = a->max_norm;
   d.norm_sq = a->norm_sq; d.sample_size = a->sample_size; d.stats_out = a->stats_out; d.zero_grad = a->zero_grad;
+  d.sample_size_f32 = a->sample_size_f32; d.hyper_dev = a->hyper_dev;
   adadelta_flat_kernel<<<elementwise_grid(n, 256), 256, 0, (cudaStream_t)stream>>>(p, g, sq, acc, (__nv_bfloat16*)p_bf16, n, d);
   B200_LAUNCHED("adadelta_flat_kernel");
   return 0;

@@ -37,13 +37,15 @@ def _stream():
 class AdamArgs(ctypes.Structure):
     _fields_ = [("lr", c_float), ("beta1", c_float), ("beta2", c_float), ("eps", c_float), ("weight_decay", c_float),
                 ("step", c_int), ("grad_scale_mult", c_float), ("max_norm", c_float),
-                ("norm_sq", c_void_p), ("sample_size", c_void_p), ("stats_out", c_void_p), ("zero_grad", c_int)]
+                ("norm_sq", c_void_p), ("sample_size", c_void_p), ("stats_out", c_void_p), ("zero_grad", c_int),
+                ("sample_size_f32", c_void_p), ("hyper_dev", c_void_p)]
 
 
 class AdadeltaArgs(ctypes.Structure):
     _fields_ = [("lr", c_float), ("rho", c_float), ("eps", c_float), ("weight_decay", c_float),
                 ("grad_scale_mult", c_float), ("max_norm", c_float),
-                ("norm_sq", c_void_p), ("sample_size", c_void_p), ("stats_out", c_void_p), ("zero_grad", c_int)]
+                ("norm_sq", c_void_p), ("sample_size", c_void_p), ("stats_out", c_void_p), ("zero_grad", c_int),
+                ("sample_size_f32", c_void_p), ("hyper_dev", c_void_p)]
 
 
 class LnArgs(ctypes.Structure):
@@ -171,17 +173,21 @@ def sumsq(g: torch.Tensor, out: torch.Tensor, accumulate: bool = False, ws: Opti
 
 
 def adam_flat(p, g, m, v, n, *, lr, beta1, beta2, eps, weight_decay, step, grad_scale_mult=1.0, max_norm=0.0,
-              norm_sq=None, sample_size=None, stats_out=None, zero_grad=True, p_bf16=None):
-    a = AdamArgs(lr, beta1, beta2, eps, weight_decay, int(step), grad_scale_mult, max_norm, _ptr(norm_sq), _ptr(sample_size),
-                 _ptr(stats_out), int(zero_grad))
+              norm_sq=None, sample_size=None, stats_out=None, zero_grad=True, p_bf16=None, hyper_dev=None):
+    ss64 = sample_size if (sample_size is not None and sample_size.dtype == torch.float64) else None
+    ss32 = sample_size if (sample_size is not None and sample_size.dtype == torch.float32) else None
+    a = AdamArgs(lr, beta1, beta2, eps, weight_decay, int(step), grad_scale_mult, max_norm, _ptr(norm_sq), _ptr(ss64),
+                 _ptr(stats_out), int(zero_grad), _ptr(ss32), _ptr(hyper_dev))
     check(_lib().b200_adam_flat(p.data_ptr(), g.data_ptr(), m.data_ptr(), v.data_ptr(), _ptr(p_bf16), int(n), byref(a),
                                 _stream()), "b200_adam_flat")
 
 
 def adadelta_flat(p, g, sq, acc, n, *, lr, rho, eps, weight_decay, grad_scale_mult=1.0, max_norm=0.0, norm_sq=None,
-                  sample_size=None, stats_out=None, zero_grad=True, p_bf16=None):
-    a = AdadeltaArgs(lr, rho, eps, weight_decay, grad_scale_mult, max_norm, _ptr(norm_sq), _ptr(sample_size),
-                     _ptr(stats_out), int(zero_grad))
+                  sample_size=None, stats_out=None, zero_grad=True, p_bf16=None, hyper_dev=None):
+    ss64 = sample_size if (sample_size is not None and sample_size.dtype == torch.float64) else None
+    ss32 = sample_size if (sample_size is not None and sample_size.dtype == torch.float32) else None
+    a = AdadeltaArgs(lr, rho, eps, weight_decay, grad_scale_mult, max_norm, _ptr(norm_sq), _ptr(ss64),
+                     _ptr(stats_out), int(zero_grad), _ptr(ss32), _ptr(hyper_dev))
     check(_lib().b200_adadelta_flat(p.data_ptr(), g.data_ptr(), sq.data_ptr(), acc.data_ptr(), _ptr(p_bf16), int(n),
                                     byref(a), _stream()), "b200_adadelta_flat")
 

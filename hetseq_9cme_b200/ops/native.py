@@ -67,6 +67,8 @@ def _declare(lib):
     lib.b200_version.restype = c_int
     lib.b200_launch_count.restype = c_ll
     lib.b200_reset_launch_count.restype = None
+    lib.b200_add_launch_count.argtypes = [c_ll]
+    lib.b200_add_launch_count.restype = None
     lib.b200_gemm.argtypes = [ctypes.POINTER(GemmDesc), c_void_p]
     lib.b200_gemm.restype = c_int
     # every other entry point takes (pointers/ints/floats..., stream) and returns int; argtypes are
@@ -110,6 +112,10 @@ def check(rc: int, what: str = "native call"):
 
 def launch_count() -> int:
     return int(cuda_lib().b200_launch_count()) if _cuda is not None or cuda_lib_available() else 0
+
+
+def add_launch_count(n: int) -> None:
+    cuda_lib().b200_add_launch_count(int(n))
 
 
 def reset_launch_count() -> None:

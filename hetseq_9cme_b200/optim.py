@@ -149,19 +149,31 @@ class Adam(_ArenaMixin, torch.optim.Optimizer):
                     p.copy_(w)
         return loss
 
+    def hyper_values(self, step: int):
+        """[lr, bias-corrected step size, decoupled decay factor, 0] for update number ``step`` (1-based)."""
+        g = self.param_groups[0]
+        b1, b2 = g["betas"]
+        return [g["lr"], g["lr"] * math.sqrt(1.0 - b2 ** step) / (1.0 - b1 ** step), 1.0 - g["weight_decay"] * g["lr"], 0.0]
+
     def fused_step(self, *, grad_scale_mult: float = 1.0, max_norm: float = 0.0, norm_sq=None, sample_size=None,
-                   stats_out=None, zero_grad: bool = False):
+                   stats_out=None, zero_grad: bool = False, hyper_dev=None, advance: bool = True):
         """Arena update in one kernel; scale / clip coefficients are derived on the device from
-        ``norm_sq`` (sum g^2 of the unscaled gradient) and ``sample_size`` (both device tensors, optional)."""
+        ``norm_sq`` (sum g^2 of the unscaled gradient) and ``sample_size`` (both device tensors, optional).
+        ``hyper_dev`` (device float[4], see ``hyper_values``) makes the launch replayable from a CUDA graph."""
         from .ops import kernels
         g = self.param_groups[0]
-        self._global_step += 1
+        if advance:
+            self._global_step += 1
         a = self.arena
         kernels.adam_flat(a.master, a.grad, self._flat_state["exp_avg"], self._flat_state["exp_avg_sq"], a.numel,
                           lr=g["lr"], beta1=g["betas"][0], beta2=g["betas"][1], eps=g["eps"], weight_decay=g["weight_decay"],
-                          step=self._global_step, grad_scale_mult=grad_scale_mult, max_norm=max_norm, norm_sq=norm_sq,
-                          sample_size=sample_size, stats_out=stats_out, zero_grad=zero_grad, p_bf16=a.work)
-        for p in a.params:
+                          step=max(self._global_step, 1), grad_scale_mult=grad_scale_mult, max_norm=max_norm, norm_sq=norm_sq,
+                          sample_size=sample_size, stats_out=stats_out, zero_grad=zero_grad, p_bf16=a.work, hyper_dev=hyper_dev)
+        if advance:
+            self.mark_step()
+
+    def mark_step(self):
+        for p in self.arena.params:
             self.state[p]["step"] = self._global_step
 
     def load_state_dict(self, state_dict):
@@ -218,17 +230,25 @@ class Adadelta(_ArenaMixin, torch.optim.Optimizer):
                 acc.mul_(rho).addcmul_(delta, delta, value=1.0 - rho)
         return loss
 
+    def hyper_values(self, step: int):
+        return [self.param_groups[0]["lr"], 0.0, 0.0, 0.0]
+
     def fused_step(self, *, grad_scale_mult: float = 1.0, max_norm: float = 0.0, norm_sq=None, sample_size=None,
-                   stats_out=None, zero_grad: bool = False):
+                   stats_out=None, zero_grad: bool = False, hyper_dev=None, advance: bool = True):
         from .ops import kernels
         g = self.param_groups[0]
-        self._global_step += 1
+        if advance:
+            self._global_step += 1
         a = self.arena
         kernels.adadelta_flat(a.master, a.grad, self._flat_state["square_avg"], self._flat_state["acc_delta"], a.numel,
                               lr=g["lr"], rho=g["rho"], eps=g["eps"], weight_decay=g["weight_decay"],
                               grad_scale_mult=grad_scale_mult, max_norm=max_norm, norm_sq=norm_sq, sample_size=sample_size,
-                              stats_out=stats_out, zero_grad=zero_grad, p_bf16=a.work)
-        for p in a.params:
+                              stats_out=stats_out, zero_grad=zero_grad, p_bf16=a.work, hyper_dev=hyper_dev)
+        if advance:
+            self.mark_step()
+
+    def mark_step(self):
+        for p in self.arena.params:
             self.state[p]["step"] = self._global_step
 
     def load_state_dict(self, state_dict):

@@ -70,7 +70,11 @@ class ParamArena:
             off += _round_up(p.numel())
         self.numel = off
         self.master = torch.zeros(off, dtype=torch.float32, device=self.device)
-        self.grad = torch.zeros(off, dtype=torch.float32, device=self.device)
+        # 64 spare floats behind the gradients: the per-step statistics vector lives there so that it can ride the
+        # same peer-memory mapping / reducer as the gradient buckets
+        self._grad_full = torch.zeros(off + ALIGN, dtype=torch.float32, device=self.device)
+        self.grad = self._grad_full[:off]
+        self.tail = self._grad_full[off:]
         self.work = torch.zeros(off, dtype=torch.bfloat16, device=self.device) if compute_dtype == torch.bfloat16 else None
 
         with torch.no_grad():

@@ -43,7 +43,7 @@ class P2PReducer(BaseReducer):
             raise RuntimeError("P2PReducer needs CUDA")
         if world_size > MAX_RANKS:
             raise RuntimeError("P2PReducer supports at most %d ranks (one NVSwitch domain)" % MAX_RANKS)
-        if len(arena.buckets) > MAX_BUCKETS:
+        if len(arena.buckets) + 1 > MAX_BUCKETS:
             raise RuntimeError("too many buckets for the flag array")
         self.lib = native.cuda_lib()
         _declare(self.lib)
@@ -108,6 +108,14 @@ class P2PReducer(BaseReducer):
 
     def _wait_all(self):
         torch.cuda.current_stream().wait_stream(self._side)
+
+    def reduce_tail(self):
+        """One-shot peer reduction of the statistics vector behind the gradients (64 floats), on the training stream."""
+        a = self.arena
+        native.check(self.lib.b200_p2p_allreduce(self.data_ptrs, self.flag_ptrs, self.counter.data_ptr(), self.rank,
+                                                 self.world_size, a.numel, a.tail.numel(), len(a.buckets), MAX_BUCKETS,
+                                                 self.epochs.data_ptr(), 1, 1, torch.cuda.current_stream().cuda_stream),
+                     "b200_p2p_allreduce(tail)")
 
     def all_reduce_flat(self):
         """Reduce the whole arena now (used by tests / when nothing was announced)."""

@@ -75,6 +75,11 @@ class BaseReducer(GradSink):
     def _wait_all(self):
         raise NotImplementedError
 
+    def reduce_tail(self):
+        """Sum the statistics vector (``arena.tail``) over ranks, in stream order on the training stream."""
+        if self.world_size > 1:
+            dist.all_reduce(self.arena.tail)
+
     def broadcast_parameters(self):
         """Make every rank start from rank 0's parameters (what DDP does at construction)."""
         if self.world_size > 1:

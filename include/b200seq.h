@@ -21,6 +21,8 @@ int b200_version(void);
 /* number of kernel launches issued through this library by the calling process (for gpu_launches). */
 long long b200_launch_count(void);
 void b200_reset_launch_count(void);
+/* a CUDA-graph replay re-issues launches that were counted once at capture time: add them explicitly */
+void b200_add_launch_count(long long n);
 
 /* ------------------------------------------------------------------------------------------------
  * GEMM: D[M,N] = epilogue(alpha * sum_k A(m,k) * B(n,k))      tcgen05.mma + TMEM + TMA, persistent.
@@ -78,6 +80,9 @@ typedef struct {
   const double* sample_size; /* device: optional denominator */
   float* stats_out;          /* device (or mapped pinned) float[3]: gnorm, applied scale, clipped flag */
   int zero_grad;             /* 1: leave g zeroed for the next accumulation */
+  const float* sample_size_f32; /* device: fp32 alternative to sample_size */
+  const float* hyper_dev;    /* device float[4] {lr, lr*sqrt(1-b2^t)/(1-b1^t), 1 - wd*lr, -}: when set, these override
+                              * lr/step so that a captured CUDA graph can be replayed with a new schedule value */
 } b200_adam_args;
 int b200_adam_flat(float* p, float* g, float* m, float* v, void* p_bf16 /* optional bf16 mirror */, long long n,
                    const b200_adam_args* a, void* stream);
@@ -89,6 +94,8 @@ typedef struct {
   const double* sample_size;
   float* stats_out;
   int zero_grad;
+  const float* sample_size_f32;
+  const float* hyper_dev;    /* device float[4] {lr, -, -, -} */
 } b200_adadelta_args;
 int b200_adadelta_flat(float* p, float* g, float* square_avg, float* acc_delta, void* p_bf16, long long n,
                        const b200_adadelta_args* a, void* stream);

@@ -444,6 +444,39 @@ colsum_partial_kernel(const T* __restrict__ x, long long ldx, int rows, int cols
     *reinterpret_cast<float4*>(scratch + (long long)blockIdx.y * cols + c) = t;
   }
 }
+// single-pass variant: the block's 128 column sums go straight into out[] with vector reductions at L2
+template <typename T>
+__global__ void __launch_bounds__(256)
+colsum_atomic_kernel(const T* __restrict__ x, long long ldx, int rows, int cols, int rows_per_block, float* __restrict__ out) {
+  __shared__ float4 red[8][32];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int c = blockIdx.x * 128 + lane * 4;
+  const int r0 = blockIdx.y * rows_per_block;
+  const int r1 = min(rows, r0 + rows_per_block);
+  f4 acc = {0.f, 0.f, 0.f, 0.f};
+  if (c < cols) {
+    int r = r0 + warp;
+    for (; r + 24 < r1; r += 32) {
+      const f4 v0 = load4<T>(x + (long long)r * ldx + c), v1 = load4<T>(x + (long long)(r + 8) * ldx + c);
+      const f4 v2 = load4<T>(x + (long long)(r + 16) * ldx + c), v3 = load4<T>(x + (long long)(r + 24) * ldx + c);
+      acc.x += (v0.x + v1.x) + (v2.x + v3.x); acc.y += (v0.y + v1.y) + (v2.y + v3.y);
+      acc.z += (v0.z + v1.z) + (v2.z + v3.z); acc.w += (v0.w + v1.w) + (v2.w + v3.w);
+    }
+    for (; r < r1; r += 8) {
+      const f4 v = load4<T>(x + (long long)r * ldx + c);
+      acc.x += v.x; acc.y += v.y; acc.z += v.z; acc.w += v.w;
+    }
+  }
+  red[warp][lane] = make_float4(acc.x, acc.y, acc.z, acc.w);
+  __syncthreads();
+  if (warp == 0 && c < cols) {
+    float4 t = red[0][lane];
+#pragma unroll
+    for (int w = 1; w < 8; ++w) { t.x += red[w][lane].x; t.y += red[w][lane].y; t.z += red[w][lane].z; t.w += red[w][lane].w; }
+    red_add_f4(out + c, f4{t.x, t.y, t.z, t.w});
+  }
+}
+
 __global__ void __launch_bounds__(256)
 colsum_final_kernel(const float* __restrict__ scratch, int nparts, int cols, float* __restrict__ out) {
   const int c = blockIdx.x * blockDim.x + threadIdx.x;
@@ -630,9 +663,18 @@ extern "C" long long b200_colsum_scratch_bytes(int rows, int cols) {
 
 extern "C" int b200_colsum(int dtype, const void* x, long long ldx, int rows, int cols, float* out, void* scratch,
                            long long scratch_bytes, void* stream) {
-  if (!x || !out || !scratch) return fail(B200_ERR_ARG, "colsum: null pointer");
+  if (!x || !out) return fail(B200_ERR_ARG, "colsum: null pointer");
   if (cols & 3) return fail(B200_ERR_UNSUPPORTED, "colsum: cols must be a multiple of 4");
   const int parts = rows >= 2048 ? 64 : (rows >= 256 ? 16 : 1);
+  if (scratch == nullptr) {
+    // no scratch given: one kernel, partial sums added to out[] with fp32 reductions (summation order varies)
+    if ((reinterpret_cast<uintptr_t>(out) & 15) != 0) return fail(B200_ERR_ARG, "colsum: out must be 16-byte aligned");
+    const int rpb0 = (rows + parts - 1) / parts;
+    dim3 grid0((cols + 127) / 128, parts);
+    DISPATCH_T(dtype, (colsum_atomic_kernel<T><<<grid0, 256, 0, (cudaStream_t)stream>>>((const T*)x, ldx, rows, cols, rpb0, out)));
+    B200_LAUNCHED("colsum_atomic_kernel");
+    return 0;
+  }
   if (scratch_bytes < (long long)parts * cols * 4) return fail(B200_ERR_ARG, "colsum: scratch too small");
   const int rpb = (rows + parts - 1) / parts;
   dim3 grid((cols + 127) / 128, parts);

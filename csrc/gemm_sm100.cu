@@ -503,17 +503,49 @@ static int gemm_impl(const b200_gemm_desc* d, cudaStream_t stream) {
   const int num_m = (d->M + kBM - 1) / kBM;
 
   int splits = 1;
+  int joint_bn = 0;
   if (d->accumulate) {
     splits = d->splits;
     if (splits <= 0) {
-      // auto split-K: fill the machine when the output has few tiles, keep >= 8 k-blocks per split
-      const int base_bn = d->bn > 0 ? d->bn : 128;
-      const long long tiles = (long long)num_m * ((d->N + base_bn - 1) / base_bn);
-      splits = (int)(num_sms() / (tiles > 0 ? tiles : 1));
-      if (splits < 1) splits = 1;
-      const int max_by_k = kb_total / 8 > 0 ? kb_total / 8 : 1;
-      if (splits > max_by_k) splits = max_by_k;
-      if (splits > 16) splits = 16;
+      // weight gradients: pick (BN, split-K) together so that the tile count fills whole waves of SMs.
+      // cost ~ waves x (k-blocks per split x tile width + epilogue); >= 8 k-blocks per split.
+      const int cands[4] = {256, 192, 128, 64};
+      double best = 1e30;
+      splits = 1;
+      const int nb = (d->batch0 > 1 ? d->batch0 : 1) * (d->batch1 > 1 ? d->batch1 : 1);
+      for (int ci = 0; ci < 4; ++ci) {
+        const int bn = cands[ci];
+        if (d->bn > 0 && bn != d->bn) continue;
+        const long long base = (long long)num_m * ((d->N + bn - 1) / bn) * nb;
+        for (int sp = 1; sp <= 16; ++sp) {
+          if (sp > 1 && kb_total / sp < 8) break;
+          const long long tiles = base * sp;
+          const long long waves = (tiles + num_sms() - 1) / num_sms();
+          const int kbs = (kb_total + sp - 1) / sp;
+          const double width = bn == 64 ? 96.0 : (double)bn;
+          const double cost = (double)waves * ((double)kbs * width + 6.0 * bn + 400.0);
+          if (cost < best - 1e-9) { best = cost; splits = sp; joint_bn = bn; }
+        }
+      }
+    }
+  }
+  // Skinny outputs with a long reduction (e.g. the MLM decoder dgrad: 640 x 768 over K = 30522) would leave most
+  // SMs idle: zero the output and let several CTAs per tile add their K-slices with the TMA reduce-add store.
+  bool auto_split = false;
+  int forced_bn = 0;
+  if (!d->accumulate && !out_bf16 && d->act == B200_ACT_NONE && d->aux_mode == B200_AUX_NONE && !d->D2 &&
+      (d->batch0 <= 1 && d->batch1 <= 1) && d->splits >= 0) {
+    const long long tiles128 = (long long)num_m * ((d->N + 127) / 128);
+    if (tiles128 * 2 <= num_sms() && kb_total >= 64) {
+      int sp = (int)(num_sms() / tiles128);
+      if (sp > kb_total / 16) sp = kb_total / 16;
+      if (sp > 16) sp = 16;
+      if (sp >= 2) {
+        splits = sp;
+        auto_split = true;
+        forced_bn = d->bn > 0 ? d->bn : 128;
+        B200_CUDA(cudaMemset2DAsync(d->D, (size_t)d->ldd * os, 0, (size_t)d->N * os, (size_t)d->M, stream));
+      }
     }
   }
   int kb_per_split = (kb_total + splits - 1) / splits;
@@ -523,7 +555,8 @@ static int gemm_impl(const b200_gemm_desc* d, cudaStream_t stream) {
   const int nb1 = d->batch1 > 0 ? d->batch1 : 1;
   const int nbatch = nb0 * nb1;
   if (nbatch > 1 && (d->bias || d->aux || d->D2)) return fail(B200_ERR_UNSUPPORTED, "gemm: batched mode has no bias/aux/D2 epilogue");
-  const int bn = d->bn > 0 ? d->bn : choose_bn(d->M, d->N, splits, nbatch);
+  const int bn = forced_bn > 0 ? forced_bn
+                               : (d->bn > 0 ? d->bn : (joint_bn > 0 ? joint_bn : choose_bn(d->M, d->N, splits, nbatch)));
   if (bn != 64 && bn != 128 && bn != 192 && bn != 256) return fail(B200_ERR_ARG, "gemm: bn must be 64/128/192/256");
 
   CUtensorMap tA, tB, tD, tD2;
@@ -563,7 +596,7 @@ static int gemm_impl(const b200_gemm_desc* d, cudaStream_t stream) {
   a.ldaux = d->ldaux;
   a.act = d->act;
   a.aux_mode = d->aux_mode;
-  a.accumulate = d->accumulate;
+  a.accumulate = d->accumulate || auto_split;
   a.has_d2 = d->D2 != nullptr;
   a.alpha = d->alpha;
 

@@ -359,13 +359,18 @@ def head_bwd(dl, x, w, dx=None, accumulate_dx=False, dw=None, db=None):
                                _stream()), "b200_head_bwd")
 
 
-def colsum_(x, out, ws: Optional[Workspace] = None):
-    """out[c] += sum_r x[r, c]  (fp32 accumulation)."""
-    ws = ws or Workspace.get(x.device)
+def colsum_(x, out, ws: Optional[Workspace] = None, deterministic: bool = False):
+    """out[c] += sum_r x[r, c]  (fp32 accumulation).  Default: single pass with fp32 reductions into ``out``;
+    ``deterministic=True``: two passes through workspace scratch with a fixed summation order."""
     rows, cols = x.shape
-    sc = ws.colsum_scratch(rows, cols)
-    check(_lib().b200_colsum(dtype_code(x.dtype), x.data_ptr(), x.stride(0), rows, cols, out.data_ptr(), sc.data_ptr(),
-                             sc.numel() * 4, _stream()), "b200_colsum")
+    if deterministic or (out.data_ptr() & 15):
+        ws = ws or Workspace.get(x.device)
+        sc = ws.colsum_scratch(rows, cols)
+        check(_lib().b200_colsum(dtype_code(x.dtype), x.data_ptr(), x.stride(0), rows, cols, out.data_ptr(), sc.data_ptr(),
+                                 sc.numel() * 4, _stream()), "b200_colsum")
+    else:
+        check(_lib().b200_colsum(dtype_code(x.dtype), x.data_ptr(), x.stride(0), rows, cols, out.data_ptr(), None, 0,
+                                 _stream()), "b200_colsum")
     return out
 
 

@@ -37,7 +37,7 @@ def _declare(lib):
 
 
 class P2PReducer(BaseReducer):
-    def __init__(self, arena, world_size: int, blocks: int = 48):
+    def __init__(self, arena, world_size: int, blocks: int = 32, tail_blocks: int = 128):
         super().__init__(arena, world_size)
         if arena.device.type != "cuda":
             raise RuntimeError("P2PReducer needs CUDA")
@@ -48,7 +48,8 @@ class P2PReducer(BaseReducer):
         self.lib = native.cuda_lib()
         _declare(self.lib)
         self.rank = dist.get_rank()
-        self.blocks = blocks
+        self.blocks = blocks              # while backward is still running (shares the SMs with the GEMMs)
+        self.tail_blocks = tail_blocks    # for buckets reduced after backward has finished
         dev = arena.device
         self.flags = torch.zeros(2 * MAX_BUCKETS * MAX_RANKS, dtype=torch.int32, device=dev)
         self.counter = torch.zeros(MAX_BUCKETS, dtype=torch.int32, device=dev)
@@ -104,7 +105,8 @@ class P2PReducer(BaseReducer):
         one_shot = 1 if n * 4 <= ONE_SHOT_BYTES else 0
         native.check(self.lib.b200_p2p_allreduce(self.data_ptrs, self.flag_ptrs, self.counter.data_ptr(), self.rank,
                                                  self.world_size, s, n, bi, MAX_BUCKETS, self.epochs.data_ptr(), one_shot,
-                                                 self.blocks, self._side.cuda_stream), "b200_p2p_allreduce")
+                                                 self.tail_blocks if self._after_backward else self.blocks,
+                                                 self._side.cuda_stream), "b200_p2p_allreduce")
 
     def _wait_all(self):
         torch.cuda.current_stream().wait_stream(self._side)

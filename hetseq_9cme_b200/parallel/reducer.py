@@ -35,6 +35,7 @@ class BaseReducer(GradSink):
         self._active = False
         self._expected = {bi: len({id(p) for p in ms}) for bi, (_, _, ms) in enumerate(arena.buckets)}
         self._seen = set()
+        self._after_backward = False
         self.exposed_ms = 0.0
 
     # ---- step protocol ---------------------------------------------------------------------------
@@ -62,9 +63,11 @@ class BaseReducer(GradSink):
         """After backward: reduce whatever was not announced (unused parameters, torch-autograd-only models),
         then make the training stream wait for all reductions."""
         if self._active:
+            self._after_backward = True           # nothing competes for the SMs any more: back ends may go wide
             for bi in range(len(self.arena.buckets)):
                 if bi not in self._launched:
                     self._launch(bi)
+            self._after_backward = False
             self._wait_all()
         self._active = False
 

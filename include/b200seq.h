@@ -174,7 +174,9 @@ int b200_act_bwd(int dtype, const void* dy, const void* aux, void* out, long lon
 /* y = x * keep_mask/(1-p) (n % 4 == 0); the same call on a gradient is the backward */
 int b200_dropout(int dtype, const void* x, void* y, long long n, float p, const unsigned long long* seed_dev,
                  unsigned long long stream_id, void* stream);
-/* out[c] += sum_r x[r][c]; scratch >= b200_colsum_scratch_bytes(rows, cols), no init needed */
+/* out[c] += sum_r x[r][c]; scratch >= b200_colsum_scratch_bytes(rows, cols), no init needed (deterministic
+ * two-pass).  scratch == NULL selects a single-pass variant that adds block partials to out[] with fp32
+ * reductions at L2 (order of additions varies from run to run). */
 long long b200_colsum_scratch_bytes(int rows, int cols);
 int b200_colsum(int dtype, const void* x, long long ldx, int rows, int cols, float* out, void* scratch,
                 long long scratch_bytes, void* stream);

@@ -48,8 +48,9 @@ class P2PReducer(BaseReducer):
         self.lib = native.cuda_lib()
         _declare(self.lib)
         self.rank = dist.get_rank()
-        self.blocks = blocks              # while backward is still running (shares the SMs with the GEMMs)
-        self.tail_blocks = tail_blocks    # for buckets reduced after backward has finished
+        import os
+        self.blocks = int(os.environ.get("B200_P2P_BLOCKS", blocks))            # while backward is still running
+        self.tail_blocks = int(os.environ.get("B200_P2P_TAIL_BLOCKS", tail_blocks))  # after backward has finished
         dev = arena.device
         self.flags = torch.zeros(2 * MAX_BUCKETS * MAX_RANKS, dtype=torch.int32, device=dev)
         self.counter = torch.zeros(MAX_BUCKETS, dtype=torch.int32, device=dev)

@@ -138,3 +138,42 @@ def test_ner_and_bert_cli_runs_on_cpu(tmp_path):
             "--num-workers", "0", "--log-format", "none", "--update-freq", "2", "--fast-stat-sync"]
     c3 = train.main(options.parse_training_args(argv))
     assert c3.get_num_updates() == 4 and os.path.exists(d + "/ck3/checkpoint_best.pt")
+
+
+def test_seqeval_lite_and_ner_eval(tmp_path):
+    from hetseq_9cme_b200 import seqeval_lite as se
+    yt = [["O", "B-PER", "I-PER", "O", "B-LOC"], ["B-ORG", "O"]]
+    yp = [["O", "B-PER", "I-PER", "O", "O"], ["B-ORG", "B-LOC"]]
+    assert se.get_entities(yt[0]) == {("PER", 1, 2), ("LOC", 4, 4)}
+    assert se.precision_score(yt, yp) == pytest.approx(2 / 3) and se.recall_score(yt, yp) == pytest.approx(2 / 3)
+    assert se.f1_score(yt, yp) == pytest.approx(2 / 3) and se.accuracy_score(yt, yp) == pytest.approx(5 / 7)
+    # end-to-end: train a tiny tagger for a few steps, evaluate the checkpoint
+    from hetseq_9cme_b200 import eval_bert_fine_tuning_ner, options, train
+    from hetseq_9cme_b200.data import synthetic
+    d = str(tmp_path)
+    paths = synthetic.make_conll(d, n_train=32, n_valid=8, n_test=8, vocab_words=40)
+    cfg = synthetic.write_bert_config(os.path.join(d, "c.json"), vocab_size=45, **CFG)
+    argv = ["--task", "BertForTokenClassification", "--data", d, "--dict", paths["vocab"], "--config_file", cfg,
+            "--train_file", paths["train"], "--test_file", paths["test"], "--cpu", "--max-sentences", "8", "--lr", "1e-3",
+            "--valid-subset", "test", "--save-dir", d + "/ck", "--max-epoch", "1", "--distributed-world-size", "1",
+            "--num-workers", "0", "--log-format", "none"]
+    train.main(options.parse_training_args(argv))
+    out = eval_bert_fine_tuning_ner.evaluate(d + "/ck/checkpoint_last.pt", cfg, paths["vocab"], paths["test"], device="cpu")
+    assert set(out) == {"accuracy_score", "precision", "recall", "f1"} and 0.0 <= out["accuracy_score"] <= 1.0
+
+
+def test_file_utils_and_legacy_loader(tmp_path):
+    from hetseq_9cme_b200 import file_utils
+    from hetseq_9cme_b200.data import synthetic
+    from hetseq_9cme_b200.data.BERT_DATA import CombineBertData
+    p = tmp_path / "a.bin"; p.write_bytes(b"x")
+    assert file_utils.cached_path(str(p)) == str(p) and file_utils.cached_path("file://" + str(p)) == str(p)
+    with pytest.raises(EnvironmentError):
+        file_utils.cached_path("https://s3.amazonaws.com/models/bert.tar.gz", cache_dir=str(tmp_path))
+    name = file_utils.url_to_filename("https://x/y", "etag")
+    (tmp_path / name).write_bytes(b"z")
+    assert file_utils.cached_path("https://x/y", cache_dir=str(tmp_path)).endswith(name)
+    d = synthetic.make_bert_shards(str(tmp_path / "s"), n_train_files=2, samples_per_file=5, seq_len=16, max_pred=3, vocab_size=100, test_samples=2)
+    files = sorted(os.path.join(d, f) for f in os.listdir(d) if "train" in f)
+    ds = CombineBertData(files)
+    assert len(ds) == 10 and len(ds[3]) == 6 and ds[3][0].shape == (16,)

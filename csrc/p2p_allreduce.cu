@@ -34,6 +34,8 @@ struct P2PArgs {
   int max_buckets;
   unsigned int* epoch_dev;         // local: per-bucket epoch words (advanced by the kernel itself)
   int one_shot;
+  float* sq_out;                   // local, optional: += sum of squares of the reduced values this rank produced
+  float* mc;                       // multicast (NVLS) address of the arena, or null
 };
 
 __device__ __forceinline__ void st_release_sys(unsigned int* p, unsigned int v) {
@@ -51,6 +53,33 @@ __device__ __forceinline__ float4 ld_peer_f4(const float* p) {
 }
 __device__ __forceinline__ void st_peer_f4(float* p, const float4& v) {
   asm volatile("st.global.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(p), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w) : "memory");
+}
+
+// NVLS: the switch performs the sum over all ranks' copies / replicates a store to all ranks
+__device__ __forceinline__ float4 multimem_ld_reduce_f4(const float* mc) {
+  float4 v;
+  asm volatile("multimem.ld_reduce.relaxed.sys.global.add.v4.f32 {%0, %1, %2, %3}, [%4];"
+               : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(mc) : "memory");
+  return v;
+}
+__device__ __forceinline__ void multimem_st_f4(float* mc, const float4& v) {
+  asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(mc), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w) : "memory");
+}
+
+__device__ __forceinline__ float block_sum(float v) {
+  __shared__ float red[kP2PThreads / 32];
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = v;
+  __syncthreads();
+  float t = 0.f;
+  if (threadIdx.x < 32) {
+    t = threadIdx.x < kP2PThreads / 32 ? red[threadIdx.x] : 0.f;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) t += __shfl_xor_sync(0xffffffffu, t, o);
+  }
+  __syncthreads();
+  return t;   // valid in thread 0
 }
 
 __device__ __forceinline__ void wait_flag(const unsigned int* p, unsigned int epoch) {
@@ -116,11 +145,39 @@ p2p_allreduce_kernel(const P2PArgs a) {
     if (t < a.world && t != a.rank) wait_flag(a.flags[a.rank] + flag_index(1, a.bucket, t, a.max_buckets), epoch);
     __syncthreads();
     if (i < n4) *reinterpret_cast<float4*>(a.data[a.rank] + e) = acc;
+    if (a.sq_out != nullptr && (a.bucket % a.world) == a.rank) {       // one rank accounts for a small bucket's norm
+      const float s = block_sum(i < n4 ? acc.x * acc.x + acc.y * acc.y + acc.z * acc.z + acc.w * acc.w : 0.f);
+      if (t == 0) atomicAdd(a.sq_out, s);
+    }
     return;
   }
 
   // ---- two-shot: reduce my slice over all ranks, push the result to every rank -----------------------------
-  {
+  float sq = 0.f;
+  if (a.mc != nullptr) {
+    // NVLS: one multimem.ld_reduce pulls the 8-way sum out of the switch, one multimem.st replicates it to all
+    // ranks: S/W in + S/W out per GPU instead of (W-1)/W * S each way.
+    const long long per = ((n4 + a.world - 1) / a.world);
+    const long long lo = per * a.rank, hi = (lo + per < n4) ? lo + per : n4;
+    const long long stride = (long long)gridDim.x * blockDim.x;
+    constexpr int U = 4;
+    for (long long i0 = lo + (long long)blockIdx.x * blockDim.x + t; i0 < hi; i0 += U * stride) {
+      float4 v[U];
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        const long long i = i0 + u * stride;
+        if (i < hi) v[u] = multimem_ld_reduce_f4(a.mc + a.start + (i << 2));
+      }
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        const long long i = i0 + u * stride;
+        if (i < hi) {
+          multimem_st_f4(a.mc + a.start + (i << 2), v[u]);
+          sq += v[u].x * v[u].x + v[u].y * v[u].y + v[u].z * v[u].z + v[u].w * v[u].w;
+        }
+      }
+    }
+  } else {
     const long long per = ((n4 + a.world - 1) / a.world);
     const long long lo = per * a.rank, hi = (lo + per < n4) ? lo + per : n4;
     const long long stride = (long long)gridDim.x * blockDim.x;
@@ -149,9 +206,14 @@ p2p_allreduce_kernel(const P2PArgs a) {
 #pragma unroll
           for (int p = 0; p < kMaxRanks; ++p)
             if (p < a.world) st_peer_f4(a.data[p] + e, acc);
+          sq += acc.x * acc.x + acc.y * acc.y + acc.z * acc.z + acc.w * acc.w;
         }
       }
     }
+  }
+  if (a.sq_out != nullptr) {
+    const float s = block_sum(sq);
+    if (t == 0) atomicAdd(a.sq_out, s);
   }
 
   // ---- completion: when the kernel retires, every peer has finished reading from and writing to this rank ----
@@ -220,7 +282,7 @@ extern "C" int b200_ipc_close(void* base) {
 
 extern "C" int b200_p2p_allreduce(void* const* data_ptrs, void* const* flag_ptrs, void* counter, int rank, int world,
                                   long long start, long long n, int bucket, int max_buckets, void* epoch_dev,
-                                  int one_shot, int blocks, void* stream) {
+                                  int one_shot, int blocks, float* sq_out, void* multicast_base, void* stream) {
   if (!data_ptrs || !flag_ptrs || !counter || !epoch_dev) return fail(B200_ERR_ARG, "p2p_allreduce: null pointer");
   if (world < 2 || world > kMaxRanks || rank < 0 || rank >= world) return fail(B200_ERR_ARG, "p2p_allreduce: bad rank/world %d/%d", rank, world);
   if ((start & 3) || (n & 3)) return fail(B200_ERR_ARG, "p2p_allreduce: range must be a multiple of 4 elements");
@@ -233,6 +295,8 @@ extern "C" int b200_p2p_allreduce(void* const* data_ptrs, void* const* flag_ptrs
   a.counter = static_cast<unsigned int*>(counter);
   a.rank = rank; a.world = world; a.start = start; a.n = n; a.bucket = bucket; a.max_buckets = max_buckets;
   a.epoch_dev = static_cast<unsigned int*>(epoch_dev); a.one_shot = one_shot;
+  a.sq_out = sq_out;
+  a.mc = one_shot ? nullptr : static_cast<float*>(multicast_base);
   if (blocks <= 0) blocks = 32;
   if (one_shot) {
     const long long need = ((n >> 2) + kP2PThreads - 1) / kP2PThreads;

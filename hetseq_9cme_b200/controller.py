@@ -129,8 +129,12 @@ class Controller:
         params = [p for p in model.parameters() if p.requires_grad]
         groups = model.arena_groups() if hasattr(model, "arena_groups") else None
         bucket_bytes = int(getattr(self.args, "bucket_cap_mb", 25)) * 1024 * 1024
+        grad_alloc = None
+        if self.cuda and self.world_size > 1 and getattr(self.args, "comm", "auto") in ("auto", "p2p"):
+            from .parallel.p2p import symmetric_grad_alloc
+            grad_alloc = symmetric_grad_alloc          # NVLS-capable memory when the platform offers it
         self._arena = ParamArena(params, groups=groups, device=self.device, compute_dtype=compute_dtype,
-                                 bucket_bytes=bucket_bytes)
+                                 bucket_bytes=bucket_bytes, grad_alloc=grad_alloc)
         self._reducer = build_reducer(self.args, self._arena, self.world_size)
         use_native = self.cuda and not getattr(self.args, "no_native", False) and self.precision != "fp32"
         if hasattr(model, "bind_arena"):
@@ -426,8 +430,13 @@ class Controller:
         reducer.finish()
         if self.world_size > 1:
             reducer.reduce_tail()
-        kernels.sumsq(arena.grad, ws.norm_sq, ws=ws)
-        opt.fused_step(grad_scale_mult=1.0, max_norm=float(getattr(self.args, "clip_norm", 0.0)), norm_sq=ws.norm_sq,
+        if getattr(reducer, "fused_norm", False):
+            from .parallel.p2p import SQ_SLOT
+            norm_sq = tail[SQ_SLOT:SQ_SLOT + 1]       # summed over ranks by reduce_tail: no separate norm pass
+        else:
+            kernels.sumsq(arena.grad, ws.norm_sq, ws=ws)
+            norm_sq = ws.norm_sq
+        opt.fused_step(grad_scale_mult=1.0, max_norm=float(getattr(self.args, "clip_norm", 0.0)), norm_sq=norm_sq,
                        sample_size=tail[2:3], stats_out=ws.step_stats, zero_grad=True, hyper_dev=self._g_hyper, advance=False)
         self._g_out[0:5] = tail[0:5].double()
         self._g_out[5:7] = ws.step_stats[0:3:2].double()

@@ -30,7 +30,8 @@ def _round_up(n: int, a: int = ALIGN) -> int:
 
 class ParamArena:
     def __init__(self, params: Sequence[torch.nn.Parameter], groups: Optional[Iterable[Sequence[torch.nn.Parameter]]] = None,
-                 device=None, compute_dtype: torch.dtype = torch.float32, bucket_bytes: int = 25 * 1024 * 1024):
+                 device=None, compute_dtype: torch.dtype = torch.float32, bucket_bytes: int = 25 * 1024 * 1024,
+                 grad_alloc=None):
         params = [p for p in params if p.requires_grad]
         seen = set()
         uniq = []
@@ -72,7 +73,14 @@ class ParamArena:
         self.master = torch.zeros(off, dtype=torch.float32, device=self.device)
         # 64 spare floats behind the gradients: the per-step statistics vector lives there so that it can ride the
         # same peer-memory mapping / reducer as the gradient buckets
-        self._grad_full = torch.zeros(off + ALIGN, dtype=torch.float32, device=self.device)
+        # (``grad_alloc(numel)`` lets the reducer supply memory it can share with peers, e.g. a symmetric allocation)
+        self._grad_full = None
+        if grad_alloc is not None:
+            self._grad_full = grad_alloc(off + ALIGN)
+        if self._grad_full is None:
+            self._grad_full = torch.zeros(off + ALIGN, dtype=torch.float32, device=self.device)
+        else:
+            self._grad_full.zero_()
         self.grad = self._grad_full[:off]
         self.tail = self._grad_full[off:]
         self.work = torch.zeros(off, dtype=torch.bfloat16, device=self.device) if compute_dtype == torch.bfloat16 else None

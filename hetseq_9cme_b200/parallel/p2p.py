@@ -22,6 +22,31 @@ from .reducer import BaseReducer
 MAX_BUCKETS = 512
 MAX_RANKS = 8
 ONE_SHOT_BYTES = 256 * 1024
+NVLS_MIN_BYTES = 1 << 20          # below this the two barriers dominate; peer loads are as fast
+SQ_SLOT = 8                       # arena.tail[SQ_SLOT] accumulates this rank's share of sum(g^2)
+
+_symm = {"handle": None, "tensor": None}
+
+
+def symmetric_grad_alloc(numel: int):
+    """Try to place the gradient arena in torch symmetric memory so that an NVLS multicast mapping exists
+    (``multimem.ld_reduce`` / ``multimem.st``).  Returns None when unavailable; the reducer then maps peers with
+    plain CUDA IPC and uses the peer load/store kernel only."""
+    import os
+    if os.environ.get("B200_NO_NVLS"):
+        return None
+    try:
+        import torch.distributed._symmetric_memory as symm_mem
+        t = symm_mem.empty(numel, dtype=torch.float32, device=torch.device("cuda", torch.cuda.current_device()))
+        hdl = symm_mem.rendezvous(t, dist.group.WORLD)
+        _symm["handle"], _symm["tensor"] = hdl, t
+        return t
+    except Exception as e:  # no fabric / multicast support in this environment
+        from ..distributed_utils import log_all
+        if dist.get_rank() == 0:
+            log_all("| symmetric memory unavailable ({}: {}); NVLS path disabled".format(type(e).__name__, str(e)[:120]))
+        _symm["handle"] = _symm["tensor"] = None
+        return None
 
 
 def _declare(lib):
@@ -32,7 +57,7 @@ def _declare(lib):
     lib.b200_ipc_open.restype = I
     lib.b200_ipc_close.argtypes = [P]
     lib.b200_ipc_close.restype = I
-    lib.b200_p2p_allreduce.argtypes = [ctypes.POINTER(P), ctypes.POINTER(P), P, I, I, LL, LL, I, I, P, I, I, P]
+    lib.b200_p2p_allreduce.argtypes = [ctypes.POINTER(P), ctypes.POINTER(P), P, I, I, LL, LL, I, I, P, I, I, P, P, P]
     lib.b200_p2p_allreduce.restype = I
 
 
@@ -63,8 +88,18 @@ class P2PReducer(BaseReducer):
             native.check(self.lib.b200_ipc_export(t.data_ptr(), buf, ctypes.byref(off)), "b200_ipc_export")
             return bytes(buf.raw), int(off.value)
 
-        mine = {"rank": self.rank, "grad": export(arena.grad), "flags": export(self.flags), "numel": arena.numel,
-                "host": _hostname()}
+        # gradients in symmetric memory are already mapped by torch's rendezvous (VMM memory has no legacy IPC
+        # handle); otherwise export the cudaMalloc'ed arena ourselves
+        hdl = _symm["handle"]
+        use_symm = (hdl is not None and _symm["tensor"] is not None
+                    and _symm["tensor"].data_ptr() == arena._grad_full.data_ptr())
+        symm_ptrs = None
+        if use_symm:
+            symm_ptrs = [int(p) for p in hdl.buffer_ptrs]
+            own_off = arena._grad_full.data_ptr() - symm_ptrs[self.rank]
+            symm_ptrs = [p + own_off for p in symm_ptrs]
+        mine = {"rank": self.rank, "grad": None if use_symm else export(arena.grad), "flags": export(self.flags),
+                "numel": arena.numel, "host": _hostname()}
         gathered: List[dict] = [None] * world_size
         dist.all_gather_object(gathered, mine)
         if any(g["numel"] != arena.numel for g in gathered):
@@ -81,12 +116,29 @@ class P2PReducer(BaseReducer):
                 flag_ptrs[r] = self.flags.data_ptr()
                 continue
             for key, arr in (("grad", data_ptrs), ("flags", flag_ptrs)):
+                if key == "grad" and use_symm:
+                    arr[r] = symm_ptrs[r]
+                    continue
                 handle, off = g[key]
                 p, base = ctypes.c_void_p(), ctypes.c_void_p()
                 native.check(self.lib.b200_ipc_open(handle, off, ctypes.byref(p), ctypes.byref(base)), "b200_ipc_open")
                 arr[r] = p.value
                 self._opened.append(base.value)
         self.data_ptrs, self.flag_ptrs = data_ptrs, flag_ptrs
+        # NVLS: multicast address of the arena when it lives in symmetric memory
+        self.mc_base = 0
+        if use_symm:
+            try:
+                mc = int(hdl.multicast_ptr or 0)
+                self.mc_base = mc + own_off if mc else 0
+            except Exception:
+                self.mc_base = 0
+        self.fused_norm = True            # bucket kernels add sum(g^2) of their slice into arena.tail[SQ_SLOT]
+        self.sq_ptr = arena.tail[SQ_SLOT:SQ_SLOT + 1].data_ptr()
+        if self.rank == 0:
+            from ..distributed_utils import log_all
+            log_all("| p2p reducer: {} ranks, {} buckets, NVLS multicast {}".format(
+                world_size, len(arena.buckets), "on" if self.mc_base else "off"))
         self.epoch = 0
         self._side = torch.cuda.Stream(device=dev)
         dist.barrier()
@@ -104,10 +156,11 @@ class P2PReducer(BaseReducer):
         ev.record(torch.cuda.current_stream())
         self._side.wait_event(ev)
         one_shot = 1 if n * 4 <= ONE_SHOT_BYTES else 0
+        mc = self.mc_base if (self.mc_base and n * 4 >= NVLS_MIN_BYTES) else 0
         native.check(self.lib.b200_p2p_allreduce(self.data_ptrs, self.flag_ptrs, self.counter.data_ptr(), self.rank,
                                                  self.world_size, s, n, bi, MAX_BUCKETS, self.epochs.data_ptr(), one_shot,
                                                  self.tail_blocks if self._after_backward else self.blocks,
-                                                 self._side.cuda_stream), "b200_p2p_allreduce")
+                                                 self.sq_ptr, mc, self._side.cuda_stream), "b200_p2p_allreduce")
 
     def _wait_all(self):
         torch.cuda.current_stream().wait_stream(self._side)
@@ -117,8 +170,8 @@ class P2PReducer(BaseReducer):
         a = self.arena
         native.check(self.lib.b200_p2p_allreduce(self.data_ptrs, self.flag_ptrs, self.counter.data_ptr(), self.rank,
                                                  self.world_size, a.numel, a.tail.numel(), len(a.buckets), MAX_BUCKETS,
-                                                 self.epochs.data_ptr(), 1, 1, torch.cuda.current_stream().cuda_stream),
-                     "b200_p2p_allreduce(tail)")
+                                                 self.epochs.data_ptr(), 1, 1, None, None,
+                                                 torch.cuda.current_stream().cuda_stream), "b200_p2p_allreduce(tail)")
 
     def all_reduce_flat(self):
         """Reduce the whole arena now (used by tests / when nothing was announced)."""

@@ -36,6 +36,7 @@ class BaseReducer(GradSink):
         self._expected = {bi: len({id(p) for p in ms}) for bi, (_, _, ms) in enumerate(arena.buckets)}
         self._seen = set()
         self._after_backward = False
+        self.fused_norm = False           # True: reductions leave sum(g^2) in arena.tail (no separate norm pass)
         self.exposed_ms = 0.0
 
     # ---- step protocol ---------------------------------------------------------------------------

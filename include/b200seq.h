@@ -220,7 +220,9 @@ int b200_ipc_close(void* base);
  * launch it, each on its own GPU. */
 int b200_p2p_allreduce(void* const* data_ptrs, void* const* flag_ptrs, void* counter, int rank, int world,
                        long long start, long long n, int bucket, int max_buckets, void* epoch_dev, int one_shot,
-                       int blocks, void* stream);
+                       int blocks, float* sq_out /* optional local fp32: += sum of squares of what this rank reduced */,
+                       void* multicast_base /* optional NVLS multicast address of the arena: multimem.ld_reduce / .st */,
+                       void* stream);
 
 #ifdef __cplusplus
 }

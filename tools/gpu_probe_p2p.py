@@ -19,19 +19,28 @@ def main():
     torch.manual_seed(0)
     sizes = [3, 64 * 7, 1000, 65536 * 2, 1 << 20, (1 << 22) + 64, 30522 * 768, 768 * 3072, 768 * 3072, 768 * 3072, 2304 * 768]
     params = [torch.nn.Parameter(torch.zeros(s, device="cuda")) for s in sizes]
-    arena = ParamArena(params, device="cuda", bucket_bytes=8 * 1024 * 1024)
+    from hetseq_9cme_b200.parallel.p2p import SQ_SLOT, symmetric_grad_alloc
+    arena = ParamArena(params, device="cuda", bucket_bytes=8 * 1024 * 1024, grad_alloc=symmetric_grad_alloc)
     red = P2PReducer(arena, world)
+    if rank == 0:
+        print("multicast base: %#x" % red.mc_base, flush=True)
     ok = True
     for step in range(4):
         g = torch.Generator(device="cuda").manual_seed(100 * step + rank)
         arena.grad.copy_(torch.randn(arena.numel, device="cuda", generator=g))
         ref = arena.grad.clone()
         dist.all_reduce(ref)
+        arena.tail.zero_()
         red.begin(True)
         if step % 2 == 0:
             red.ready(list(reversed(arena.params)))      # announce in backward order -> per-bucket launches
         red.finish()
+        red.reduce_tail()
         torch.cuda.synchronize()
+        nsq, nsq_ref = arena.tail[SQ_SLOT].item(), ref.double().pow(2).sum().item()
+        if rank == 0:
+            print("  fused sum(g^2) %.6e vs %.6e" % (nsq, nsq_ref), flush=True)
+        ok = ok and abs(nsq - nsq_ref) < 1e-4 * nsq_ref
         err = (arena.grad - ref).abs().max().item() / ref.abs().max().item()
         same = torch.tensor([arena.grad.double().sum().item()], device="cuda", dtype=torch.float64)
         lo, hi = same.clone(), same.clone()

@@ -60,9 +60,27 @@ class BaseReducer(GradSink):
             if self._remaining[bi] == 0:
                 self._launch(bi)
 
+    def enable_timing(self, on: bool = True):
+        """Measure, per step, how long the training stream has to wait for reductions after backward is done
+        (the *exposed* all-reduce time).  Uses timing events, so it cannot be on while a CUDA graph is captured."""
+        self._timing = on and self.arena.device.type == "cuda"
+        self._timing_pairs = []
+
+    def exposed_ms(self):
+        """Mean exposed wait per timed step (call after a synchronize)."""
+        pairs = getattr(self, "_timing_pairs", [])
+        if not pairs:
+            return None
+        vals = [max(0.0, a.elapsed_time(b)) for a, b in pairs]
+        return sum(vals) / len(vals)
+
     def finish(self):
         """After backward: reduce whatever was not announced (unused parameters, torch-autograd-only models),
         then make the training stream wait for all reductions."""
+        timing = getattr(self, "_timing", False) and self._active
+        if timing:
+            e_bwd = torch.cuda.Event(enable_timing=True)
+            e_bwd.record(torch.cuda.current_stream())          # backward is complete at this point of the stream
         if self._active:
             self._after_backward = True           # nothing competes for the SMs any more: back ends may go wide
             for bi in range(len(self.arena.buckets)):
@@ -70,6 +88,10 @@ class BaseReducer(GradSink):
                     self._launch(bi)
             self._after_backward = False
             self._wait_all()
+            if timing:
+                e_red = torch.cuda.Event(enable_timing=True)
+                e_red.record(torch.cuda.current_stream())      # ... and here every reduction has landed
+                self._timing_pairs.append((e_bwd, e_red))
         self._active = False
 
     # ---- back-end hooks --------------------------------------------------------------------------

@@ -16,6 +16,7 @@
 //   * kind::tf32 consumes fp32 storage directly (fp32/TF32 parity mode); kind::f16 consumes bf16.
 #include "common.h"
 #include "sm100_ptx.cuh"
+#include "vec_utils.cuh"
 #include "../include/b200seq.h"
 
 #include <mutex>
@@ -37,6 +38,14 @@ struct GemmArgs {
   long long ldaux;
   int act, aux_mode, accumulate, has_d2;
   float alpha;
+  // attention-softmax epilogues (single N tile): 1 = P = softmax(alpha*acc + mask) [+ dropout copy to D2],
+  // 2 = dS = P * (dPe - rowsum(P*dPe)) with P read as aux and dPe = acc through the regenerated dropout mask
+  int epi_mode;
+  const long long* attn_mask;
+  float p_drop;
+  const unsigned long long* seed_dev;
+  unsigned long long stream_id;
+  long long ldp;                 // row pitch of the probability tensors (dropout element index)
 };
 
 constexpr int kBM = 128;
@@ -58,7 +67,7 @@ __device__ __forceinline__ float to_f<float>(float v) { return v; }
 template <>
 __device__ __forceinline__ float to_f<__nv_bfloat16>(__nv_bfloat16 v) { return __bfloat162float(v); }
 
-template <typename TIn, typename TOut, int BN, bool A_MN, bool B_MN, int STAGES>
+template <typename TIn, typename TOut, int BN, bool A_MN, bool B_MN, int STAGES, bool EPI_SOFTMAX>
 __global__ void __launch_bounds__(kGemmThreads, 1)
 gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                     const __grid_constant__ CUtensorMap tmD, const __grid_constant__ CUtensorMap tmD2,
@@ -207,12 +216,14 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
     // from, one chunk ahead of the math; the row-owner then reads its 128 B row from swizzled smem.
     const bool tma_aux = (args.aux_mode != B200_AUX_NONE) && !args.has_d2;
     uint64_t* my_aux_bar = aux_bar + ew * 2;
+    int cur_b0 = 0, cur_b1 = 0;
     auto issue_aux = [&](int nc_, int m0_, uint32_t ev_) {       // lane 0 only
       tma_store_wait_read<0>();                                  // every earlier store has left its buffer
       uint64_t* bar = &my_aux_bar[ev_ & 1];
       mbar_arrive_expect_tx(bar, kStageBufBytes);
-      tma_load_4d(stg + (ev_ & 1) * kStageBufBytes, &tmAux, bar, nc_, m0_, 0, 0);
+      tma_load_4d(stg + (ev_ & 1) * kStageBufBytes, &tmAux, bar, nc_, m0_, cur_b0, cur_b1);
     };
+    uint32_t ax = 0;                       // aux-tile sequence counter of the softmax-backward epilogue
 
     for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++tcount) {
       const int split = tile % args.splits;
@@ -227,6 +238,153 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
       tcgen05_fence_after();
       const int row = m0 + q * 32 + lane;
       const bool add_bias = (bias != nullptr) && (split == 0);
+      cur_b0 = b0; cur_b1 = b1;
+      if constexpr (EPI_SOFTMAX) {
+        // ======================= attention softmax epilogues (whole row inside this tile) =======================
+        const bool live = (m0 + q * 32 < args.M);
+        const int NCH = (args.N + CW - 1) / CW;
+        const long long rowg = ((long long)bt * args.M + row) * args.ldp;      // element index of (row, 0)
+        const Philox ph(args.seed_dev ? *args.seed_dev : 0ull);
+        const uint32_t thr = dropout_threshold(args.p_drop);
+        const float ik = args.p_drop > 0.f ? 1.f / (1.f - args.p_drop) : 1.f;
+        const uint32_t tbase = tmem_base + ((uint32_t)(q * 32) << 16) + acc * ACC_STRIDE;
+        auto load_chunk = [&](int c, float (&v)[CW]) {
+#pragma unroll
+          for (int h = 0; h < CW / 32; ++h) {
+            uint32_t r[32];
+            tmem_ld_32x32(tbase + c * CW + h * 32, r);
+            tmem_ld_wait();
+#pragma unroll
+            for (int j = 0; j < 32; ++j) v[h * 32 + j] = __uint_as_float(r[j]);
+          }
+        };
+        auto store_chunk = [&](const CUtensorMap* tm, const float (&v)[CW], int c, uint32_t bufsel) {
+          uint8_t* buf = stg + (bufsel & 1) * kStageBufBytes;
+          if (lane == 0) tma_store_wait_read<1>();
+          __syncwarp();
+          uint8_t* rowp = buf + lane * 128;
+#pragma unroll
+          for (int i = 0; i < 8; ++i) {
+            uint4 u;
+            if constexpr (OS == 4) {
+              u.x = __float_as_uint(v[4 * i + 0]); u.y = __float_as_uint(v[4 * i + 1]);
+              u.z = __float_as_uint(v[4 * i + 2]); u.w = __float_as_uint(v[4 * i + 3]);
+            } else {
+              __nv_bfloat162 p0 = __floats2bfloat162_rn(v[8 * i + 0], v[8 * i + 1]);
+              __nv_bfloat162 p1 = __floats2bfloat162_rn(v[8 * i + 2], v[8 * i + 3]);
+              __nv_bfloat162 p2 = __floats2bfloat162_rn(v[8 * i + 4], v[8 * i + 5]);
+              __nv_bfloat162 p3 = __floats2bfloat162_rn(v[8 * i + 6], v[8 * i + 7]);
+              u.x = *reinterpret_cast<uint32_t*>(&p0); u.y = *reinterpret_cast<uint32_t*>(&p1);
+              u.z = *reinterpret_cast<uint32_t*>(&p2); u.w = *reinterpret_cast<uint32_t*>(&p3);
+            }
+            *reinterpret_cast<uint4*>(rowp + ((i ^ (lane & 7)) << 4)) = u;
+          }
+          fence_proxy_async_smem();
+          __syncwarp();
+          if (lane == 0) {
+            tma_store_4d(tm, buf, n0 + c * CW, m0 + q * 32, b0, b1);
+            tma_store_commit();
+          }
+        };
+        if (live && args.epi_mode == 1) {
+          // ---- forward: online (max, sum) over the row, then normalise, optionally write the dropped copy ----
+          const long long* mrow = args.attn_mask ? args.attn_mask + (long long)b1 * args.N : nullptr;
+          float m = -3.0e38f, l = 0.f;
+#pragma unroll 1
+          for (int c = 0; c < NCH; ++c) {
+            float v[CW];
+            load_chunk(c, v);
+            float cm = -3.0e38f;
+#pragma unroll
+            for (int j = 0; j < CW; ++j) {
+              const int col = c * CW + j;
+              const float madd = (mrow && col < args.N) ? (1.f - (float)__ldg(mrow + col)) * -10000.f : 0.f;
+              v[j] = col < args.N ? v[j] * args.alpha + madd : -3.0e38f;
+              cm = fmaxf(cm, v[j]);
+            }
+            const float mn = fmaxf(m, cm);
+            float sum = 0.f;
+#pragma unroll
+            for (int j = 0; j < CW; ++j) sum += (c * CW + j < args.N) ? __expf(v[j] - mn) : 0.f;
+            l = l * __expf(m - mn) + sum;
+            m = mn;
+          }
+          const float inv = 1.f / l;
+#pragma unroll 1
+          for (int c = 0; c < NCH; ++c) {
+            float v[CW];
+            load_chunk(c, v);
+#pragma unroll
+            for (int j = 0; j < CW; ++j) {
+              const int col = c * CW + j;
+              const float madd = (mrow && col < args.N) ? (1.f - (float)__ldg(mrow + col)) * -10000.f : 0.f;
+              v[j] = col < args.N ? __expf(v[j] * args.alpha + madd - m) * inv : 0.f;
+            }
+            store_chunk(&tmD, v, c, ev++);
+            if (args.has_d2) {
+#pragma unroll
+              for (int j = 0; j < CW; j += 4) {
+                const f4 d = dropout_scale4(ph, (unsigned long long)(rowg + c * CW + j), args.stream_id, thr, ik);
+                v[j] *= d.x; v[j + 1] *= d.y; v[j + 2] *= d.z; v[j + 3] *= d.w;
+              }
+              store_chunk(&tmD2, v, c, ev++);
+            }
+          }
+        } else if (live) {
+          // ---- backward: two passes over (acc = dP, aux = P); aux tiles stream through the staging buffers ----
+          auto aux_issue = [&](int c, uint32_t seq) {           // lane 0 only
+            tma_store_wait_read<0>();
+            uint64_t* bar = &my_aux_bar[seq & 1];
+            mbar_arrive_expect_tx(bar, kStageBufBytes);
+            tma_load_4d(stg + (seq & 1) * kStageBufBytes, &tmAux, bar, n0 + c * CW, m0 + q * 32, b0, b1);
+          };
+          auto aux_read = [&](uint32_t seq, float (&pv)[CW]) {
+            mbar_wait(&my_aux_bar[seq & 1], (seq >> 1) & 1);
+            const uint8_t* rowp = stg + (seq & 1) * kStageBufBytes + lane * 128;
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+              const uint4 u = *reinterpret_cast<const uint4*>(rowp + ((i ^ (lane & 7)) << 4));
+              const TOut* a = reinterpret_cast<const TOut*>(&u);
+#pragma unroll
+              for (int e = 0; e < 16 / OS; ++e) pv[i * (16 / OS) + e] = to_f<TOut>(a[e]);
+            }
+            __syncwarp();
+          };
+          if (lane == 0) aux_issue(0, ax);
+          float dot = 0.f;
+#pragma unroll 1
+          for (int pass = 0; pass < 2; ++pass) {
+#pragma unroll 1
+            for (int c = 0; c < NCH; ++c) {
+              float pv[CW], v[CW];
+              aux_read(ax, pv);
+              const bool more = !(pass == 1 && c == NCH - 1);
+              if (lane == 0 && more) aux_issue(c + 1 < NCH ? c + 1 : 0, ax + 1);
+              load_chunk(c, v);
+              if (args.p_drop > 0.f) {
+#pragma unroll
+                for (int j = 0; j < CW; j += 4) {
+                  const f4 d = dropout_scale4(ph, (unsigned long long)(rowg + c * CW + j), args.stream_id, thr, ik);
+                  v[j] *= d.x; v[j + 1] *= d.y; v[j + 2] *= d.z; v[j + 3] *= d.w;
+                }
+              }
+              if (pass == 0) {
+#pragma unroll
+                for (int j = 0; j < CW; ++j) dot += pv[j] * v[j];
+              } else {
+#pragma unroll
+                for (int j = 0; j < CW; ++j) v[j] = pv[j] * (v[j] - dot);
+                store_chunk(&tmD, v, c, ax);
+              }
+              ++ax;
+            }
+          }
+        }
+        tcgen05_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&tmem_empty[acc]);
+        continue;
+      }
       if (tma_aux && lane == 0 && n0 < args.N && m0 + q * 32 < args.M) issue_aux(n0, m0 + q * 32, ev);
 
 #pragma unroll 1
@@ -424,7 +582,23 @@ static int launch_gemm(const CUtensorMap& tA, const CUtensorMap& tB, const CUten
                        const CUtensorMap& tX, const GemmArgs& args, cudaStream_t stream) {
   constexpr int STAGES = stages_for<BN>();
   constexpr int smem = STAGES * (kBM * 128 + BN * 128) + kEpiBytes + 1024 /*align*/ + (2 * STAGES + 12) * 8 + 16;
-  auto kern = gemm_tcgen05_kernel<TIn, TOut, BN, A_MN, B_MN, STAGES>;
+  if constexpr (!A_MN && !B_MN && sizeof(TIn) == sizeof(TOut)) {
+    if (args.epi_mode != 0) {        // attention-softmax epilogue kernels are separate instantiations
+      auto kern_sm = gemm_tcgen05_kernel<TIn, TOut, BN, A_MN, B_MN, STAGES, true>;
+      static bool attr_set_sm = false;
+      if (!attr_set_sm) {
+        B200_CUDA(cudaFuncSetAttribute(kern_sm, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+        attr_set_sm = true;
+      }
+      const long long tiles_sm = (long long)args.nbatch * args.num_m * args.num_n * args.splits;
+      const int grid_sm = tiles_sm < num_sms() ? (int)tiles_sm : num_sms();
+      kern_sm<<<grid_sm, kGemmThreads, smem, stream>>>(tA, tB, tD, tD2, tX, args);
+      B200_LAUNCHED("gemm_tcgen05_kernel<softmax>");
+      return 0;
+    }
+  }
+  if (args.epi_mode != 0) return fail(B200_ERR_UNSUPPORTED, "gemm: softmax epilogues need K-major operands and matching in/out dtype");
+  auto kern = gemm_tcgen05_kernel<TIn, TOut, BN, A_MN, B_MN, STAGES, false>;
   static bool attr_set = false;
   if (!attr_set) {
     B200_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
@@ -554,9 +728,20 @@ static int gemm_impl(const b200_gemm_desc* d, cudaStream_t stream) {
   const int nb0 = d->batch0 > 0 ? d->batch0 : 1;
   const int nb1 = d->batch1 > 0 ? d->batch1 : 1;
   const int nbatch = nb0 * nb1;
-  if (nbatch > 1 && (d->bias || d->aux || d->D2)) return fail(B200_ERR_UNSUPPORTED, "gemm: batched mode has no bias/aux/D2 epilogue");
-  const int bn = forced_bn > 0 ? forced_bn
-                               : (d->bn > 0 ? d->bn : (joint_bn > 0 ? joint_bn : choose_bn(d->M, d->N, splits, nbatch)));
+  const int epi_mode = d->epi_mode;
+  if (epi_mode == 0 && nbatch > 1 && (d->bias || d->aux || d->D2))
+    return fail(B200_ERR_UNSUPPORTED, "gemm: batched mode has no bias/aux/D2 epilogue");
+  if (epi_mode != 0) {
+    if (epi_mode != 1 && epi_mode != 2) return fail(B200_ERR_ARG, "gemm: unknown epi_mode %d", epi_mode);
+    if (d->N > 256) return fail(B200_ERR_UNSUPPORTED, "gemm: softmax epilogues need the whole row in one tile (N <= 256)");
+    if (d->accumulate || d->bias || d->act) return fail(B200_ERR_ARG, "gemm: softmax epilogues take no bias/act/accumulate");
+    if (epi_mode == 2 && !d->aux) return fail(B200_ERR_ARG, "gemm: softmax-backward epilogue needs the probabilities as aux");
+    if (d->p_drop > 0.f && !d->seed_dev) return fail(B200_ERR_ARG, "gemm: dropout needs seed_dev");
+    if (epi_mode == 1 && d->p_drop > 0.f && !d->D2) return fail(B200_ERR_ARG, "gemm: softmax with dropout needs D2 for the dropped copy");
+  }
+  int bn = forced_bn > 0 ? forced_bn
+                         : (d->bn > 0 ? d->bn : (joint_bn > 0 ? joint_bn : choose_bn(d->M, d->N, splits, nbatch)));
+  if (epi_mode != 0) bn = d->N <= 64 ? 64 : (d->N <= 128 ? 128 : (d->N <= 192 ? 192 : 256));
   if (bn != 64 && bn != 128 && bn != 192 && bn != 256) return fail(B200_ERR_ARG, "gemm: bn must be 64/128/192/256");
 
   CUtensorMap tA, tB, tD, tD2;
@@ -571,14 +756,14 @@ static int gemm_impl(const b200_gemm_desc* d, cudaStream_t stream) {
   rc = make_tmap_4d(&tD, d->D, os, out_bf16, d->M, d->N, d->ldd, CW, 32, false, nb0, d->sd0, nb1, d->sd1);
   if (rc) return rc;
   if (d->D2) {
-    rc = make_tmap_4d(&tD2, d->D2, os, out_bf16, d->M, d->N, d->ldd, CW, 32, false, 1, 0, 1, 0);
+    rc = make_tmap_4d(&tD2, d->D2, os, out_bf16, d->M, d->N, d->ldd, CW, 32, false, nb0, d->sd0, nb1, d->sd1);
     if (rc) return rc;
   } else {
     tD2 = tD;
   }
   CUtensorMap tX = tD;
   if (d->aux) {
-    rc = make_tmap_4d(&tX, d->aux, os, out_bf16, d->M, d->N, d->ldaux, CW, 32, false, 1, 0, 1, 0);
+    rc = make_tmap_4d(&tX, d->aux, os, out_bf16, d->M, d->N, d->ldaux, CW, 32, false, nb0, d->sd0, nb1, d->sd1);
     if (rc) return rc;
   }
 
@@ -599,6 +784,13 @@ static int gemm_impl(const b200_gemm_desc* d, cudaStream_t stream) {
   a.accumulate = d->accumulate || auto_split;
   a.has_d2 = d->D2 != nullptr;
   a.alpha = d->alpha;
+  a.epi_mode = epi_mode;
+  a.attn_mask = d->attn_mask;
+  a.p_drop = d->p_drop;
+  a.seed_dev = d->seed_dev;
+  a.stream_id = d->stream_id;
+  a.ldp = d->ldd;
+  if (epi_mode != 0) a.aux_mode = B200_AUX_NONE;     // aux is consumed by the softmax-backward epilogue itself
 
   switch (d->dtype) {
     case B200_F32_TF32: return dispatch_bn<float, float>(bn, d->a_mn, d->b_mn, tA, tB, tD, tD2, tX, a, stream);

@@ -191,6 +191,10 @@ ln_bwd_kernel(const LnCommon<T> a, const T* __restrict__ dy, long long lddy, con
 }
 
 
+struct LnDirect {
+  float* dgamma; float* dbeta; float* dbias;
+};
+
 // Two warps per row: halves the per-thread column accumulators (register pressure was capping the one-warp
 // version at one block per SM).  Block = 8 warps = 4 rows per iteration; row statistics are combined through
 // shared memory (double-buffered by iteration parity -> one __syncthreads per iteration).  cols % 256 == 0.
@@ -198,7 +202,7 @@ template <typename T, int NVH>
 __global__ void __launch_bounds__(kLnThreads, 2)
 ln_bwd2_kernel(const LnCommon<T> a, const T* __restrict__ dy, long long lddy, const float* __restrict__ mean_in,
                const float* __restrict__ rstd_in, T* __restrict__ ds, long long ldds, T* __restrict__ dz, long long lddz,
-               float* __restrict__ scratch, int want_dbias) {
+               float* __restrict__ scratch, int want_dbias, const LnDirect direct) {
   extern __shared__ float red[];            // [4 row-slots][cols] for the final fold
   __shared__ float2 part[2][4][2];          // [parity][row slot][half]
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -280,7 +284,9 @@ ln_bwd2_kernel(const LnCommon<T> a, const T* __restrict__ dy, long long lddy, co
     }
   }
 
-  float* out = scratch + (long long)blockIdx.x * 3 * a.cols;
+  // block fold; then either per-block partials to scratch (deterministic two-pass, finalize kernel follows) or,
+  // when direct != nullptr, fp32 reductions straight into the parameter gradients (one launch less)
+  float* out = scratch ? scratch + (long long)blockIdx.x * 3 * a.cols : nullptr;
 #pragma unroll 1
   for (int qn = 0; qn < 3; ++qn) {
     if (qn == 2 && !want_dbias) break;
@@ -292,8 +298,12 @@ ln_bwd2_kernel(const LnCommon<T> a, const T* __restrict__ dy, long long lddy, co
       *reinterpret_cast<float4*>(red + slot * a.cols + c) = make_float4(t.x, t.y, t.z, t.w);
     }
     __syncthreads();
-    for (int c = threadIdx.x; c < a.cols; c += kLnThreads)
-      out[qn * a.cols + c] = red[c] + red[a.cols + c] + red[2 * a.cols + c] + red[3 * a.cols + c];
+    float* dst = qn == 0 ? direct.dgamma : (qn == 1 ? direct.dbeta : direct.dbias);
+    for (int c = threadIdx.x; c < a.cols; c += kLnThreads) {
+      const float t = red[c] + red[a.cols + c] + red[2 * a.cols + c] + red[3 * a.cols + c];
+      if (out) out[qn * a.cols + c] = t;
+      else atomicAdd(dst + c, t);
+    }
   }
 }
 
@@ -371,9 +381,11 @@ static int ln_bwd_t(const b200_ln_args* a, cudaStream_t st) {
     if (blocks < 1) blocks = 1;
     const size_t smem2 = (size_t)4 * a->cols * sizeof(float);
     const int want = a->dbias != nullptr;
+    const bool direct_mode = a->scratch == nullptr;
+    const LnDirect direct{a->dgamma, a->dbeta, a->dbias};
 #define LN_BWD2(NVH)                                                                                                  \
   ln_bwd2_kernel<T, NVH><<<blocks, kLnThreads, smem2, st>>>(c, (const T*)a->dy, a->lddy, a->mean, a->rstd, (T*)a->ds,  \
-                                                            a->ldds, (T*)a->dz, a->lddz, (float*)a->scratch, want)
+                                                            a->ldds, (T*)a->dz, a->lddz, (float*)a->scratch, want, direct)
     switch (a->cols / 256) {
       case 1: LN_BWD2(1); break;
       case 2: LN_BWD2(2); break;
@@ -382,6 +394,7 @@ static int ln_bwd_t(const b200_ln_args* a, cudaStream_t st) {
     }
 #undef LN_BWD2
     B200_LAUNCHED("ln_bwd2_kernel");
+    if (direct_mode) return 0;
     dim3 grid2((a->cols + 31) / 32, 3);
     ln_bwd_finalize<<<grid2, 256, 0, st>>>((const float*)a->scratch, blocks, a->cols, a->dgamma, a->dbeta, a->dbias);
     B200_LAUNCHED("ln_bwd_finalize");
@@ -420,8 +433,10 @@ extern "C" int b200_ln_fwd(const b200_ln_args* a, void* stream) {
 extern "C" int b200_ln_bwd(const b200_ln_args* a, void* stream) {
   int rc = check_ln(a);
   if (rc) return rc;
-  if (!a->dy || !a->mean || !a->rstd || !a->dgamma || !a->dbeta || !a->scratch)
+  if (!a->dy || !a->mean || !a->rstd || !a->dgamma || !a->dbeta)
     return fail(B200_ERR_ARG, "layernorm bwd: null pointer");
-  if (a->scratch_bytes < b200_ln_bwd_scratch_bytes(a->cols)) return fail(B200_ERR_ARG, "layernorm bwd: scratch too small");
+  if (!a->scratch && (a->cols & 255))
+    return fail(B200_ERR_ARG, "layernorm bwd: scratch may be omitted only when cols is a multiple of 256");
+  if (a->scratch && a->scratch_bytes < b200_ln_bwd_scratch_bytes(a->cols)) return fail(B200_ERR_ARG, "layernorm bwd: scratch too small");
   return a->dtype == 0 ? ln_bwd_t<float>(a, (cudaStream_t)stream) : ln_bwd_t<__nv_bfloat16>(a, (cudaStream_t)stream);
 }

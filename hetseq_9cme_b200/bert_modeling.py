@@ -380,7 +380,8 @@ class BertPreTrainedModel(nn.Module):
                 print("| native kernels disabled for this model: {}".format(why), flush=True)
                 self._native_notice = True
             return None
-        return bert_native.NativeCtx(input_ids.device, self.training, self._grad_sink)
+        return bert_native.NativeCtx(input_ids.device, self.training, self._grad_sink,
+                                     checkpoint_activations=getattr(self, "checkpoint_activations", False) and self.training)
 
     @classmethod
     def from_pretrained(cls, path, *inputs, **kwargs):
@@ -449,7 +450,7 @@ class _HeadModel(BertPreTrainedModel):
             seq2d, pooled = self.bert.native_forward(nctx, input_ids, token_type_ids, attention_mask, want_pooled)
             return seq2d.view(B, L, -1), pooled
         seq, pooled = self.bert(input_ids, token_type_ids, attention_mask, output_all_encoded_layers=False,
-                                checkpoint_activations=checkpoint_activations)
+                                checkpoint_activations=checkpoint_activations or getattr(self, "checkpoint_activations", False))
         return seq, pooled
 
     def bind_arena(self, arena, grad_sink=None):

@@ -141,6 +141,9 @@ class Controller:
             model.bind_arena(self._arena if use_native else None, self._reducer)
         if not use_native and hasattr(model, "force_torch_path"):
             model.force_torch_path = True
+        if getattr(self.args, "checkpoint_activations", False):
+            model.checkpoint_activations = True          # native blocks recompute; torch path uses torch.utils.checkpoint
+        self._nvtx = bool(getattr(self.args, "profile", False)) and self.cuda
         self._hook_handles = []
         if self.world_size > 1:
             # parameters that plain autograd (not a native block) produces gradients for announce themselves
@@ -273,6 +276,12 @@ class Controller:
             num_shards=self.world_size, shard_id=getattr(self.args, "distributed_rank", 0) or 0,
             num_workers=self.args.num_workers, epoch=epoch)
 
+    def _range(self, name):
+        """NVTX range for ``--profile`` (data / forward_backward / reduce_wait / update); no-op otherwise."""
+        if getattr(self, "_nvtx", False):
+            return torch.cuda.nvtx.range(name)
+        return contextlib.nullcontext()
+
     def _prepare_sample(self, sample):
         if utils.sample_is_empty(sample):
             return None
@@ -313,7 +322,8 @@ class Controller:
                 sample = self._prepare_sample(self._dummy_batch)
             reducer.begin(sync_now=(i == len(samples) - 1))
             try:
-                loss, sample_size, logging_output = self.task.train_step(sample, model, optimizer, ignore_grad)
+                with self._range("forward_backward"):
+                    loss, sample_size, logging_output = self.task.train_step(sample, model, optimizer, ignore_grad)
             except RuntimeError as e:
                 if "out of memory" in str(e):
                     raise RuntimeError("ran out of memory with exception: {}".format(e))
@@ -325,7 +335,8 @@ class Controller:
                 stat_sum[0] += _as_dev_scalar(logging_output.get("loss", 0.0), dev)
                 stat_sum[1] += _as_dev_scalar(logging_output.get("nll_loss", 0.0), dev)
                 last_logging, last_sample_size = logging_output, sample_size
-        reducer.finish()
+        with self._range("reduce_wait"):
+            reducer.finish()
         if dummy_batch:
             return None
 
@@ -355,6 +366,8 @@ class Controller:
         clip_norm = float(getattr(self.args, "clip_norm", 0.0))
         if self.cuda:
             from .ops import kernels
+            if getattr(self, "_nvtx", False):
+                torch.cuda.nvtx.range_push("update")
             ws = kernels.Workspace.get(dev)
             kernels.sumsq(self._arena.grad, ws.norm_sq, ws=ws)
             if sample_size_dev is not None:
@@ -364,6 +377,8 @@ class Controller:
             optimizer.optimizer.fused_step(grad_scale_mult=mult, max_norm=clip_norm, norm_sq=ws.norm_sq,
                                            sample_size=ss_dev, stats_out=ws.step_stats, zero_grad=True)
             stat_sum[5:7] = ws.step_stats[0:3:2].double()
+            if getattr(self, "_nvtx", False):
+                torch.cuda.nvtx.range_pop()
         else:
             if sample_size_dev is not None:
                 ss = float(sample_size_dev.item())

@@ -36,10 +36,11 @@ _NULL_SINK = GradSink()
 class NativeCtx:
     """Per-forward execution context shared by the blocks of one model call."""
 
-    def __init__(self, device, training: bool, sink: Optional[GradSink] = None):
+    def __init__(self, device, training: bool, sink: Optional[GradSink] = None, checkpoint_activations: bool = False):
         self.ws = K.Workspace.get(device)
         self.training = training
         self.sink = sink or _NULL_SINK
+        self.checkpoint_activations = checkpoint_activations
 
     @property
     def seed(self):
@@ -115,45 +116,77 @@ def _pad8(n: int) -> int:
     return (n + 7) // 8 * 8
 
 
+def _fused_softmax(L: int) -> bool:
+    """Softmax inside the GEMM epilogue needs a whole score row in one 128 x BN tile (BN <= 256)."""
+    import os
+    # measured on B200 (profiles/README.md): at L = 128 the four epilogue warps become the bottleneck and the fused
+    # form is ~6 % slower per step than the separate full-chip softmax kernels, so it is opt-in for now
+    return L <= 256 and bool(os.environ.get("B200_FUSED_SOFTMAX"))
+
+
+def _layer_forward(x, nctx, lp, attn_mask, B, L, sid, p_attn, p_hid):
+    """Forward kernels of one encoder layer; returns (output, tensors backward needs)."""
+    H = x.shape[1]
+    heads, dh = lp.heads, lp.dh
+    Lp = _pad8(L)
+    dev, dt = x.device, x.dtype
+    qkv = gemm(x, lp.Wqkv, bias=lp.bqkv)                                                    # [M, 3H]
+    S = torch.empty((B, heads, L, Lp), dtype=dt, device=dev)
+    if _fused_softmax(L):
+        # softmax (+ mask, + dropout copy) runs in the epilogue of the score GEMM: the scores never reach memory
+        Pd = torch.empty_like(S) if p_attn > 0 else S
+        bgemm(qkv, qkv, S, M=L, N=L, K=dh, lda=3 * H, ldb=3 * H, ldd=Lp, a_mn=False, b_mn=False, batch0=heads, batch1=B,
+              sa=(dh, L * 3 * H), sb=(dh, L * 3 * H), sd=(L * Lp, heads * L * Lp), b_off=H, alpha=1.0 / math.sqrt(dh),
+              epi_mode=1, attn_mask=attn_mask, p_drop=p_attn, seed=nctx.seed, stream_id=sid + 1,
+              d2=Pd if p_attn > 0 else None)
+    else:
+        bgemm(qkv, qkv, S, M=L, N=L, K=dh, lda=3 * H, ldb=3 * H, ldd=Lp, a_mn=False, b_mn=False, batch0=heads, batch1=B,
+              sa=(dh, L * 3 * H), sb=(dh, L * 3 * H), sd=(L * Lp, heads * L * Lp), b_off=H, alpha=1.0 / math.sqrt(dh))
+        Pd = K.softmax_fwd_(S, attn_mask, B, heads, L, Lp, p_attn, nctx.seed, sid + 1)       # S now holds P
+    ctxv = torch.empty((B * L, H), dtype=dt, device=dev)
+    bgemm(Pd, qkv, ctxv, M=L, N=dh, K=L, lda=Lp, ldb=3 * H, ldd=H, a_mn=False, b_mn=True, batch0=heads, batch1=B,
+          sa=(L * Lp, heads * L * Lp), sb=(dh, L * 3 * H), sd=(dh, L * H), b_off=2 * H)
+    z1 = gemm(ctxv, lp.Wo)
+    y1, mean1, rstd1 = K.ln_fwd(z1, lp.g1, lp.be1, bias=lp.bo, residual=x, eps=lp.eps, p_pre=p_hid, seed=nctx.seed,
+                                stream_pre=sid + 2)
+    u = torch.empty((B * L, lp.W1.shape[0]), dtype=dt, device=dev)
+    a = gemm(y1, lp.W1, bias=lp.b1, act=N.ACT_GELU, preact_out=u)
+    z2 = gemm(a, lp.W2)
+    y2, mean2, rstd2 = K.ln_fwd(z2, lp.g2, lp.be2, bias=lp.b2, residual=y1, eps=lp.eps, p_pre=p_hid, seed=nctx.seed,
+                                stream_pre=sid + 3)
+    return y2, (qkv, S, Pd, ctxv, z1, y1, mean1, rstd1, u, a, z2, mean2, rstd2)
+
+
 class BertLayerFn(torch.autograd.Function):
     @staticmethod
     def forward(ctx, x, nctx: NativeCtx, lp: LayerPack, attn_mask, B: int, L: int, sid: int):
         H = x.shape[1]
-        heads, dh = lp.heads, lp.dh
-        Lp = _pad8(L)
         p_attn = lp.p_attn if nctx.training else 0.0
         p_hid = lp.p_hidden if nctx.training else 0.0
-        dev, dt = x.device, x.dtype
         x = x.contiguous()
-
-        qkv = gemm(x, lp.Wqkv, bias=lp.bqkv)                                                    # [M, 3H]
-        S = torch.empty((B, heads, L, Lp), dtype=dt, device=dev)
-        bgemm(qkv, qkv, S, M=L, N=L, K=dh, lda=3 * H, ldb=3 * H, ldd=Lp, a_mn=False, b_mn=False, batch0=heads, batch1=B,
-              sa=(dh, L * 3 * H), sb=(dh, L * 3 * H), sd=(L * Lp, heads * L * Lp), b_off=H, alpha=1.0 / math.sqrt(dh))
-        Pd = K.softmax_fwd_(S, attn_mask, B, heads, L, Lp, p_attn, nctx.seed, sid + 1)           # S now holds P
-        ctxv = torch.empty((B * L, H), dtype=dt, device=dev)
-        bgemm(Pd, qkv, ctxv, M=L, N=dh, K=L, lda=Lp, ldb=3 * H, ldd=H, a_mn=False, b_mn=True, batch0=heads, batch1=B,
-              sa=(L * Lp, heads * L * Lp), sb=(dh, L * 3 * H), sd=(dh, L * H), b_off=2 * H)
-        z1 = gemm(ctxv, lp.Wo)
-        y1, mean1, rstd1 = K.ln_fwd(z1, lp.g1, lp.be1, bias=lp.bo, residual=x, eps=lp.eps, p_pre=p_hid, seed=nctx.seed,
-                                    stream_pre=sid + 2)
-        u = torch.empty((B * L, lp.W1.shape[0]), dtype=dt, device=dev)
-        a = gemm(y1, lp.W1, bias=lp.b1, act=N.ACT_GELU, preact_out=u)
-        z2 = gemm(a, lp.W2)
-        y2, mean2, rstd2 = K.ln_fwd(z2, lp.g2, lp.be2, bias=lp.b2, residual=y1, eps=lp.eps, p_pre=p_hid, seed=nctx.seed,
-                                    stream_pre=sid + 3)
-
-        ctx.nctx, ctx.lp, ctx.dims, ctx.sid, ctx.ps = nctx, lp, (B, L, Lp, H), sid, (p_attn, p_hid)
+        y2, saved = _layer_forward(x, nctx, lp, attn_mask, B, L, sid, p_attn, p_hid)
+        ctx.nctx, ctx.lp, ctx.dims, ctx.sid, ctx.ps = nctx, lp, (B, L, _pad8(L), H), sid, (p_attn, p_hid)
         ctx.attn_mask = attn_mask
-        ctx.save_for_backward(x, qkv, S, Pd, ctxv, z1, y1, mean1, rstd1, u, a, z2, mean2, rstd2)
+        ctx.recompute = bool(getattr(nctx, "checkpoint_activations", False))
+        if ctx.recompute:
+            # activation checkpointing: keep only the layer input; the forward kernels run again in backward and
+            # regenerate the very same dropout masks from (seed, call-site id, element index)
+            ctx.save_for_backward(x)
+        else:
+            ctx.save_for_backward(x, *saved)
         return y2
 
     @staticmethod
     def backward(ctx, dy2):
-        x, qkv, P, Pd, ctxv, z1, y1, mean1, rstd1, u, a, z2, mean2, rstd2 = ctx.saved_tensors
         nctx, lp, sid = ctx.nctx, ctx.lp, ctx.sid
         B, L, Lp, H = ctx.dims
         p_attn, p_hid = ctx.ps
+        if ctx.recompute:
+            (x,) = ctx.saved_tensors
+            _, saved = _layer_forward(x, nctx, lp, ctx.attn_mask, B, L, sid, p_attn, p_hid)
+            qkv, P, Pd, ctxv, z1, y1, mean1, rstd1, u, a, z2, mean2, rstd2 = saved
+        else:
+            x, qkv, P, Pd, ctxv, z1, y1, mean1, rstd1, u, a, z2, mean2, rstd2 = ctx.saved_tensors
         heads, dh = lp.heads, lp.dh
         ws = nctx.ws
         dt, dev = x.dtype, x.device
@@ -185,12 +218,18 @@ class BertLayerFn(torch.autograd.Function):
         sQ = (dh, L * 3 * H)
         sC = (dh, L * H)
         dP = torch.empty((B, heads, L, Lp), dtype=dt, device=dev)
-        bgemm(dctx, qkv, dP, M=L, N=L, K=dh, lda=H, ldb=3 * H, ldd=Lp, a_mn=False, b_mn=False, batch0=heads, batch1=B,
-              sa=sC, sb=sQ, sd=sS, b_off=2 * H)                                                   # dP = dctx V^T
+        fused = _fused_softmax(L)
+        if fused:     # dS = P * (dPe - rowsum(P*dPe)) computed in the epilogue of the dP GEMM
+            bgemm(dctx, qkv, dP, M=L, N=L, K=dh, lda=H, ldb=3 * H, ldd=Lp, a_mn=False, b_mn=False, batch0=heads, batch1=B,
+                  sa=sC, sb=sQ, sd=sS, b_off=2 * H, epi_mode=2, aux=P, p_drop=p_attn, seed=nctx.seed, stream_id=sid + 1)
+        else:
+            bgemm(dctx, qkv, dP, M=L, N=L, K=dh, lda=H, ldb=3 * H, ldd=Lp, a_mn=False, b_mn=False, batch0=heads, batch1=B,
+                  sa=sC, sb=sQ, sd=sS, b_off=2 * H)                                               # dP = dctx V^T
         dqkv = torch.empty((B * L, 3 * H), dtype=dt, device=dev)
         bgemm(Pd, dctx, dqkv, M=L, N=dh, K=L, lda=Lp, ldb=H, ldd=3 * H, a_mn=True, b_mn=True, batch0=heads, batch1=B,
               sa=sS, sb=sC, sd=sQ, d_off=2 * H)                                                   # dV = Pd^T dctx
-        K.softmax_bwd_(P, dP, B, heads, L, Lp, p_attn, nctx.seed, sid + 1)                        # dP <- dS
+        if not fused:
+            K.softmax_bwd_(P, dP, B, heads, L, Lp, p_attn, nctx.seed, sid + 1)                    # dP <- dS
         bgemm(dP, qkv, dqkv, M=L, N=dh, K=L, lda=Lp, ldb=3 * H, ldd=3 * H, a_mn=False, b_mn=True, batch0=heads, batch1=B,
               sa=sS, sb=sQ, sd=sQ, b_off=H, alpha=scale)                                          # dQ = dS K / sqrt(d)
         bgemm(dP, qkv, dqkv, M=L, N=dh, K=L, lda=Lp, ldb=3 * H, ldd=3 * H, a_mn=True, b_mn=True, batch0=heads, batch1=B,

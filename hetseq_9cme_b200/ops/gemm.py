@@ -92,6 +92,7 @@ def gemm(a: torch.Tensor, b: torch.Tensor, *, a_mn: bool = False, b_mn: bool = F
     d.act, d.aux_mode, d.accumulate, d.alpha = act, aux_mode, int(accumulate), float(alpha)
     d.bn, d.splits = bn, splits
     d.batch0 = d.batch1 = 0
+    d.epi_mode = 0
     native.check(native.cuda_lib().b200_gemm(ctypes.byref(d), _stream_ptr()), "b200_gemm")
     return out
 
@@ -99,7 +100,8 @@ def gemm(a: torch.Tensor, b: torch.Tensor, *, a_mn: bool = False, b_mn: bool = F
 def bgemm(a_ptr_t: torch.Tensor, b_ptr_t: torch.Tensor, out_t: torch.Tensor, *, M: int, N: int, K: int,
           lda: int, ldb: int, ldd: int, a_mn: bool, b_mn: bool, batch0: int, batch1: int,
           sa=(0, 0), sb=(0, 0), sd=(0, 0), a_off: int = 0, b_off: int = 0, d_off: int = 0, alpha: float = 1.0,
-          out_fp32: bool = False, bn: int = 0) -> None:
+          out_fp32: bool = False, bn: int = 0, epi_mode: int = 0, attn_mask=None, p_drop: float = 0.0, seed=None,
+          stream_id: int = 0, d2: Optional[torch.Tensor] = None, aux: Optional[torch.Tensor] = None) -> None:
     """Batched GEMM over (batch1 x batch0) problems addressed by element strides — used for attention, where
     batch0 = head and batch1 = sequence.  ``*_off`` are element offsets into the given storage tensors."""
     es = a_ptr_t.element_size()
@@ -112,9 +114,16 @@ def bgemm(a_ptr_t: torch.Tensor, b_ptr_t: torch.Tensor, out_t: torch.Tensor, *, 
     d.A, d.lda, d.a_mn = a_ptr_t.data_ptr() + a_off * es, lda, int(a_mn)
     d.B, d.ldb, d.b_mn = b_ptr_t.data_ptr() + b_off * es, ldb, int(b_mn)
     d.D, d.ldd = out_t.data_ptr() + d_off * out_t.element_size(), ldd
-    d.D2 = d.bias = d.aux = None
-    d.ldaux = 0
+    d.D2 = d2.data_ptr() if d2 is not None else None
+    d.bias = None
+    d.aux = aux.data_ptr() if aux is not None else None
+    d.ldaux = ldd if aux is not None else 0
     d.act = d.aux_mode = d.accumulate = 0
+    d.epi_mode = epi_mode
+    d.attn_mask = attn_mask.data_ptr() if attn_mask is not None else None
+    d.p_drop = float(p_drop)
+    d.seed_dev = seed.data_ptr() if seed is not None else None
+    d.stream_id = int(stream_id)
     d.alpha = float(alpha)
     d.bn, d.splits = bn, 0
     d.batch0, d.batch1 = batch0, batch1

@@ -16,6 +16,7 @@ from . import native
 from .native import check, cuda_lib
 
 FP32, BF16 = 0, 1
+_LN_TWO_PASS = bool(__import__('os').environ.get('B200_LN_TWO_PASS'))
 
 
 def dtype_code(t: torch.dtype) -> int:
@@ -236,7 +237,8 @@ def ln_fwd(x, gamma, beta, *, bias=None, residual=None, eps=1e-12, p_pre=0.0, p_
 
 
 def ln_bwd(dy, x, gamma, beta, mean, rstd, dgamma, dbeta, *, bias=None, dbias=None, residual=None, eps=1e-12, p_pre=0.0,
-           p_post=0.0, seed=None, stream_pre=0, stream_post=0, want_ds=True, want_dz=False, ws: Optional[Workspace] = None):
+           p_post=0.0, seed=None, stream_pre=0, stream_post=0, want_ds=True, want_dz=False, ws: Optional[Workspace] = None,
+           deterministic: bool = False):
     """Returns (ds, dz): ds = grad wrt the LN input (residual branch), dz = grad wrt x (through pre-dropout).
     Parameter gradients are accumulated into dgamma / dbeta / dbias (fp32)."""
     ws = ws or Workspace.get(x.device)
@@ -251,8 +253,11 @@ def ln_bwd(dy, x, gamma, beta, mean, rstd, dgamma, dbeta, *, bias=None, dbias=No
     if dz is not None:
         a.dz, a.lddz = dz.data_ptr(), dz.stride(0)
     a.dgamma, a.dbeta, a.dbias = dgamma.data_ptr(), dbeta.data_ptr(), _ptr(dbias)
-    sc = ws.ln_scratch(cols)
-    a.scratch, a.scratch_bytes = sc.data_ptr(), sc.numel() * 4
+    if deterministic or cols % 256 != 0 or _LN_TWO_PASS:
+        sc = ws.ln_scratch(cols)
+        a.scratch, a.scratch_bytes = sc.data_ptr(), sc.numel() * 4
+    else:
+        a.scratch, a.scratch_bytes = None, 0       # block partials are added to the parameter gradients directly
     check(_lib().b200_ln_bwd(byref(a), _stream()), "b200_ln_bwd")
     return ds, dz
 

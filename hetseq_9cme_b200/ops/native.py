@@ -51,6 +51,8 @@ class GemmDesc(ctypes.Structure):
         ("bn", c_int), ("splits", c_int),
         ("batch0", c_int), ("batch1", c_int),
         ("sa0", c_ll), ("sa1", c_ll), ("sb0", c_ll), ("sb1", c_ll), ("sd0", c_ll), ("sd1", c_ll),
+        ("epi_mode", c_int), ("attn_mask", c_void_p), ("p_drop", c_float), ("seed_dev", c_void_p),
+        ("stream_id", ctypes.c_ulonglong),
     ]
 
 

@@ -132,6 +132,7 @@ class LanguageModelingTask(Task):
         config = BertConfig.from_json_file(args.config_file)
         model = BertForPreTraining(config)
         model.max_predictions_per_seq = getattr(args, "max_predictions_per_seq", 0) or getattr(self, "_max_pred", 0)
+        model.checkpoint_activations = bool(getattr(args, "checkpoint_activations", False))
         return model
 
     def load_dataset(self, split, **kwargs):

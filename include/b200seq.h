@@ -54,6 +54,15 @@ typedef struct {
    * No bias / aux / D2 epilogue in batched mode. */
   int batch0, batch1;
   long long sa0, sa1, sb0, sb1, sd0, sd1;
+  /* attention epilogues (N <= 256 so that a row lives in one tile; D2 / aux share D's pitch and batch strides):
+   *   epi_mode 1: D = softmax(alpha*acc + (1-mask)*-10000) per row, D2 = dropout(D) when p_drop > 0
+   *   epi_mode 2: D = P * (dPe - rowsum(P * dPe)),  P = aux,  dPe = acc through the regenerated dropout mask
+   * ref: hetseq/bert_modeling.py:361-371 and its autograd dual */
+  int epi_mode;
+  const long long* attn_mask;            /* [batch1][N] 0/1, optional */
+  float p_drop;
+  const unsigned long long* seed_dev;
+  unsigned long long stream_id;
 } b200_gemm_desc;
 
 int b200_gemm(const b200_gemm_desc* d, void* stream);
@@ -127,7 +136,9 @@ typedef struct {
   void* ds; long long ldds;                 /* optional: grad wrt the LN input (== grad of residual) */
   void* dz; long long lddz;                 /* optional: grad wrt x (ds through the pre-dropout mask) */
   float* dgamma; float* dbeta; float* dbias;/* fp32 [cols], accumulated with +=; dbias optional */
-  void* scratch; long long scratch_bytes;   /* >= b200_ln_bwd_scratch_bytes(cols); contents need no init */
+  void* scratch; long long scratch_bytes;   /* >= b200_ln_bwd_scratch_bytes(cols); contents need no init.  May be NULL
+                                             * when cols % 256 == 0: block partials then go into dgamma/dbeta/dbias with
+                                             * fp32 atomics (one launch less, summation order varies) */
 } b200_ln_args;
 long long b200_ln_bwd_scratch_bytes(int cols);
 int b200_ln_fwd(const b200_ln_args* a, void* stream);

@@ -114,6 +114,9 @@ def test_layernorm_fwd_bwd(K, dtype, cols):
     dbias = torch.zeros(cols, device="cuda")
     ds, dz = K.ln_bwd(dy, x, gamma, beta, mean, rstd, dg, db, bias=bias, dbias=dbias, residual=res, eps=1e-12)
     assert dz is None
+    dg2, db2, dbias2 = torch.zeros(cols, device="cuda"), torch.zeros(cols, device="cuda"), torch.zeros(cols, device="cuda")
+    K.ln_bwd(dy, x, gamma, beta, mean, rstd, dg2, db2, bias=bias, dbias=dbias2, residual=res, eps=1e-12, deterministic=True)
+    assert _rel(dg2, dg) < 1e-4 and _rel(db2, db) < 1e-4 and _rel(dbias2, dbias) < 1e-4   # two-pass == atomic path
     assert _rel(ds, xr.grad) < tol
     assert _rel(dg, gr.grad) < tol
     assert _rel(db, br.grad) < tol
@@ -299,3 +302,42 @@ def test_sumsq_and_adam_match_reference_math(K):
                     max_norm=max_norm, norm_sq=ws.norm_sq, sample_size=sample, stats_out=stats, zero_grad=False)
     assert _rel(p, pr) < 1e-5
     assert abs(stats[0].item() - gnorm) / gnorm < 1e-4 and stats[2].item() == 1.0
+
+
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+@pytest.mark.parametrize("L", [128, 72])
+def test_softmax_epilogues_match_separate_kernels(K, dtype, L):
+    """Score GEMM with the softmax epilogue == plain score GEMM followed by the softmax kernel (fwd and bwd),
+    including identical dropout masks."""
+    from hetseq_9cme_b200.ops.gemm import bgemm
+    torch.manual_seed(12)
+    B, h, dh, p = 2, 3, 64, 0.1
+    H = h * dh
+    Lp = (L + 7) // 8 * 8
+    ws = K.Workspace.get("cuda")
+    ws.set_seed(4321)
+    qkv = torch.randn(B * L, 3 * H, device="cuda").to(dtype)
+    mask = torch.ones(B, L, dtype=torch.int64, device="cuda")
+    mask[1, L - 11:] = 0
+    common = dict(M=L, N=L, K=dh, lda=3 * H, ldb=3 * H, ldd=Lp, a_mn=False, b_mn=False, batch0=h, batch1=B,
+                  sa=(dh, L * 3 * H), sb=(dh, L * 3 * H), sd=(L * Lp, h * L * Lp), b_off=H, alpha=0.125)
+    S = torch.zeros(B, h, L, Lp, device="cuda", dtype=dtype)
+    bgemm(qkv, qkv, S, **common)
+    Pd_ref = K.softmax_fwd_(S, mask, B, h, L, Lp, p, ws.seed, 77)
+    P = torch.zeros_like(S); Pd = torch.zeros_like(S)
+    bgemm(qkv, qkv, P, epi_mode=1, attn_mask=mask, p_drop=p, seed=ws.seed, stream_id=77, d2=Pd, **common)
+    tol = 1e-5 if dtype == torch.float32 else 1e-2
+    assert (P[..., :L].float() - S[..., :L].float()).abs().max().item() < tol
+    assert (Pd[..., :L].float() - Pd_ref[..., :L].float()).abs().max().item() < tol * 2
+    assert ((Pd[..., :L] == 0) == (Pd_ref[..., :L] == 0)).float().mean().item() > 0.999      # same dropout mask
+    # backward: dS from the epilogue of dP = dctx V^T
+    dctx = torch.randn(B * L, H, device="cuda").to(dtype)
+    bw = dict(M=L, N=L, K=dh, lda=H, ldb=3 * H, ldd=Lp, a_mn=False, b_mn=False, batch0=h, batch1=B,
+              sa=(dh, L * H), sb=(dh, L * 3 * H), sd=(L * Lp, h * L * Lp), b_off=2 * H)
+    dP = torch.zeros_like(S)
+    bgemm(dctx, qkv, dP, **bw)
+    K.softmax_bwd_(S, dP, B, h, L, Lp, p, ws.seed, 77)
+    dS = torch.zeros_like(S)
+    bgemm(dctx, qkv, dS, epi_mode=2, aux=S, p_drop=p, seed=ws.seed, stream_id=77, **bw)
+    scale = dP[..., :L].float().abs().max().item()
+    assert (dS[..., :L].float() - dP[..., :L].float()).abs().max().item() < (1e-4 if dtype == torch.float32 else 3e-2) * scale

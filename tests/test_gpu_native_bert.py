@@ -131,3 +131,21 @@ def test_dropout_training_step_is_finite_and_seed_dependent():
     assert l1.item() == l1b.item()                 # same seed -> same masks
     assert (g1 - g1b).abs().max().item() < 1e-3 * g1.abs().max().item()   # (atomics reorder fp32 adds)
     assert l1.item() != l2.item()
+
+
+def test_activation_recompute_gives_identical_gradients():
+    cfgk = dict(hidden_size=128, num_hidden_layers=2, num_attention_heads=2, intermediate_size=512,
+                hidden_dropout_prob=0.1, attention_probs_dropout_prob=0.1, max_position_embeddings=128)
+    from hetseq_9cme_b200.ops import kernels as K
+    cfg, ref, nat, arena = _models("BertForPreTraining", cfgk)
+    ids, tts, mask, mlm, nsp = _batch(4, 128, 1000)
+    nat.train()
+    ws = K.Workspace.get("cuda")
+    ws.set_seed(9)
+    l1 = nat(ids, tts, mask, mlm, nsp); l1.backward()
+    g1 = arena.grad.clone(); arena.zero_grad()
+    nat.checkpoint_activations = True
+    ws.set_seed(9)
+    l2 = nat(ids, tts, mask, mlm, nsp); l2.backward()
+    assert l1.item() == l2.item()
+    assert (arena.grad - g1).abs().max().item() <= 1e-3 * g1.abs().max().item()

@@ -66,6 +66,15 @@ class LnArgs(ctypes.Structure):
                 ("scratch", c_void_p), ("scratch_bytes", c_longlong)]
 
 
+class AttnArgs(ctypes.Structure):
+    _fields_ = [("dtype", c_int), ("B", c_int), ("heads", c_int), ("L", c_int), ("Lp", c_int),
+                ("scale", c_float), ("p_drop", c_float),
+                ("qkv", c_void_p), ("ld_qkv", c_longlong),
+                ("attn_mask", c_void_p), ("seed_dev", c_void_p), ("stream_id", c_ulonglong),
+                ("out", c_void_p), ("ld_out", c_longlong),
+                ("lse", c_void_p), ("delta", c_void_p), ("o", c_void_p), ("dout", c_void_p), ("ld_o", c_longlong)]
+
+
 _declared = False
 
 
@@ -100,6 +109,8 @@ def _lib():
             "b200_colsum": ([I, P, LL, I, I, P, P, LL, P], I),
             "b200_softmax_fwd": ([I, P, P, P, I, I, I, I, F, P, ULL, P], I),
             "b200_softmax_bwd": ([I, P, P, I, I, I, I, F, P, ULL, P], I),
+            "b200_attn_fwd": ([POINTER(AttnArgs), P], I),
+            "b200_attn_bwd": ([POINTER(AttnArgs), P], I),
             "b200_dropout": ([I, P, P, LL, F, P, ULL, P], I),
             "b200_act_bwd": ([I, P, P, P, LL, I, P], I),
         }
@@ -391,6 +402,47 @@ def softmax_bwd_(P, dP, B, heads, L, Lp, p_drop=0.0, seed=None, stream_id=0):
     check(_lib().b200_softmax_bwd(dtype_code(P.dtype), P.data_ptr(), dP.data_ptr(), B, heads, L, Lp, float(p_drop),
                                   _ptr(seed), stream_id, _stream()), "b200_softmax_bwd")
     return dP
+
+
+def _attn_args(qkv, attn_mask, B, heads, L, Lp, scale, p_drop, seed, stream_id):
+    assert qkv.dim() == 2 and qkv.shape[0] == B * L and qkv.shape[1] == 3 * heads * 64 and qkv.stride(1) == 1
+    a = AttnArgs()
+    a.dtype = dtype_code(qkv.dtype)
+    a.B, a.heads, a.L, a.Lp = B, heads, L, Lp
+    a.scale, a.p_drop = float(scale), float(p_drop)
+    a.qkv, a.ld_qkv = qkv.data_ptr(), qkv.stride(0)
+    a.attn_mask = _ptr(attn_mask)
+    a.seed_dev = _ptr(seed)
+    a.stream_id = stream_id
+    return a
+
+
+def attn_fwd(qkv, attn_mask, B, heads, L, scale, p_drop=0.0, seed=None, stream_id=0, Lp=None, out=None):
+    """Fused attention forward on the packed projection ``qkv`` [B*L, 3*heads*64].
+
+    Returns (ctx [B*L, heads*64], lse [B*heads*L] fp32).  ref: hetseq/bert_modeling.py:341-376."""
+    Lp = Lp or (L + 3) // 4 * 4
+    a = _attn_args(qkv, attn_mask, B, heads, L, Lp, scale, p_drop, seed, stream_id)
+    if out is None:
+        out = torch.empty(B * L, heads * 64, dtype=qkv.dtype, device=qkv.device)
+    lse = torch.empty(B * heads * L, dtype=torch.float32, device=qkv.device)
+    a.out, a.ld_out, a.lse = out.data_ptr(), out.stride(0), lse.data_ptr()
+    check(_lib().b200_attn_fwd(byref(a), _stream()), "b200_attn_fwd")
+    return out, lse
+
+
+def attn_bwd(qkv, o, dout, lse, attn_mask, B, heads, L, scale, p_drop=0.0, seed=None, stream_id=0, Lp=None, out=None):
+    """Fused attention backward: returns dqkv [B*L, 3*heads*64] (every element written)."""
+    Lp = Lp or (L + 3) // 4 * 4
+    a = _attn_args(qkv, attn_mask, B, heads, L, Lp, scale, p_drop, seed, stream_id)
+    assert o.stride(1) == 1 and dout.stride(1) == 1 and o.stride(0) == dout.stride(0) and o.dtype == dout.dtype == qkv.dtype
+    if out is None:
+        out = torch.empty_like(qkv)
+    delta = torch.empty(B * heads * L, dtype=torch.float32, device=qkv.device)
+    a.out, a.ld_out, a.lse, a.delta = out.data_ptr(), out.stride(0), lse.data_ptr(), delta.data_ptr()
+    a.o, a.dout, a.ld_o = o.data_ptr(), dout.data_ptr(), o.stride(0)
+    check(_lib().b200_attn_bwd(byref(a), _stream()), "b200_attn_bwd")
+    return out
 
 
 def dropout(x, p, seed, stream_id, out=None):

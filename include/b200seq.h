@@ -217,6 +217,33 @@ int b200_softmax_bwd(int dtype, const void* P, void* dP, int B, int heads, int L
                      const unsigned long long* seed_dev, unsigned long long stream_id, void* stream);
 
 /* ------------------------------------------------------------------------------------------------
+ * Fused multi-head attention, head size 64 (tcgen05 + TMEM + TMA; no [B,heads,L,L] tensor in HBM).
+ *   forward : out[B*L, H] = dropout(softmax(Q K^T * scale + (1-mask)*-10000)) V, lse[B][heads][L] saved
+ *   backward: out = dqkv[B*L, 3H] from qkv, o (forward output), dout, lse; delta[B][heads][L] is scratch
+ * qkv is the packed projection [B*L, 3H] (Q | K | V sections, head-major inside each), H = heads*64.
+ * Dropout elements are indexed ((b*heads+h)*L + q)*Lp + k like b200_softmax_fwd, so for one seed/stream id the
+ * fused and unfused paths drop the same probabilities.
+ * ref: hetseq/bert_modeling.py:341-376 (BertSelfAttention.forward) and its autograd dual
+ * ---------------------------------------------------------------------------------------------- */
+typedef struct {
+  int dtype;                         /* 0 = fp32 storage / tf32 math, 1 = bf16 */
+  int B, heads, L, Lp;               /* Lp: row pitch used for dropout indexing (>= L, multiple of 4) */
+  float scale, p_drop;
+  const void* qkv; long long ld_qkv;
+  const long long* attn_mask;        /* [B][L] 0/1, optional */
+  const unsigned long long* seed_dev;
+  unsigned long long stream_id;
+  void* out; long long ld_out;
+  float* lse;
+  float* delta;                      /* backward only */
+  const void* o;                     /* backward only */
+  const void* dout;                  /* backward only */
+  long long ld_o;                    /* pitch of o and dout */
+} b200_attn_args;
+int b200_attn_fwd(const b200_attn_args* args, void* stream);
+int b200_attn_bwd(const b200_attn_args* args, void* stream);
+
+/* ------------------------------------------------------------------------------------------------
  * Peer-to-peer gradient all-reduce over NVLink (replaces DDP's Reducer + ncclAllReduce,
  * ref: hetseq/controller.py:79-87) and the CUDA-IPC plumbing that maps the peers' arenas.
  * ---------------------------------------------------------------------------------------------- */

@@ -341,3 +341,45 @@ def test_softmax_epilogues_match_separate_kernels(K, dtype, L):
     bgemm(dctx, qkv, dS, epi_mode=2, aux=S, p_drop=p, seed=ws.seed, stream_id=77, **bw)
     scale = dP[..., :L].float().abs().max().item()
     assert (dS[..., :L].float() - dP[..., :L].float()).abs().max().item() < (1e-4 if dtype == torch.float32 else 3e-2) * scale
+
+
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+@pytest.mark.parametrize("L,p", [(128, 0.0), (128, 0.1), (72, 0.1), (320, 0.1)])
+def test_fused_attention_matches_reference(K, dtype, L, p):
+    """Flash-style tcgen05 attention (forward + dQ/dK/dV) against fp64 PyTorch attention that applies the very same
+    dropout mask (read back from the stand-alone softmax kernel, which shares the Philox indexing)."""
+    torch.manual_seed(21)
+    B, h, dh = 2, 3, 64
+    H = h * dh
+    Lp = (L + 3) // 4 * 4
+    ws = K.Workspace.get("cuda")
+    ws.set_seed(977)
+    qkv = (torch.randn(B * L, 3 * H, device="cuda") * 0.7).to(dtype)
+    dout = torch.randn(B * L, H, device="cuda").to(dtype)
+    mask = torch.ones(B, L, dtype=torch.int64, device="cuda")
+    mask[1, L - 13:] = 0
+    scale = 1.0 / math.sqrt(dh)
+
+    keep = torch.ones(B, h, L, L, device="cuda", dtype=torch.float64)
+    if p > 0:
+        probe = torch.ones(B, h, L, Lp, device="cuda")
+        keep = (K.softmax_fwd_(probe, None, B, h, L, Lp, p, ws.seed, 33)[..., :L] != 0).double() / (1 - p)
+
+    x = qkv.double().view(B, L, 3, h, dh).requires_grad_(True)
+    q, k, v = (x[:, :, i].permute(0, 2, 1, 3) for i in range(3))
+    s = q @ k.transpose(-1, -2) * scale + ((1 - mask.double()) * -10000.0)[:, None, None, :]
+    o_ref = ((torch.softmax(s, -1) * keep) @ v).permute(0, 2, 1, 3).reshape(B * L, H)
+    o_ref.backward(dout.double())
+    dqkv_ref = x.grad.reshape(B * L, 3 * H)
+
+    o, lse = K.attn_fwd(qkv, mask, B, h, L, scale, p, ws.seed, 33, Lp=Lp)
+    dqkv = K.attn_bwd(qkv, o, dout, lse, mask, B, h, L, scale, p, ws.seed, 33, Lp=Lp)
+    torch.cuda.synchronize()
+    tol = 2e-3 if dtype == torch.float32 else 2e-2       # tf32 / bf16 operand rounding
+    assert _rel(o, o_ref) < tol
+    lse_ref = torch.logsumexp(s, -1).reshape(-1)
+    assert (lse.double() - lse_ref).abs().max().item() < (5e-3 if dtype == torch.float32 else 5e-2)
+    for i, name in enumerate("qkv"):
+        got = dqkv.view(B * L, 3, H)[:, i]
+        want = dqkv_ref.view(B * L, 3, H)[:, i]
+        assert _rel(got, want) < tol * 2, name

@@ -124,13 +124,23 @@ def _fused_softmax(L: int) -> bool:
     return L <= 256 and bool(os.environ.get("B200_FUSED_SOFTMAX"))
 
 
-def _layer_forward(x, nctx, lp, attn_mask, B, L, sid, p_attn, p_hid):
-    """Forward kernels of one encoder layer; returns (output, tensors backward needs)."""
-    H = x.shape[1]
-    heads, dh = lp.heads, lp.dh
-    Lp = _pad8(L)
-    dev, dt = x.device, x.dtype
-    qkv = gemm(x, lp.Wqkv, bias=lp.bqkv)                                                    # [M, 3H]
+def _fused_attention(L: int, dh: int) -> bool:
+    """Flash-style attention kernels (csrc/attention_sm100.cu): no [B, heads, L, L] tensor is written at all.
+
+    Measured on B200 (tools/gpu_probe_attn.py, profiles/README.md): for L <= 128 the fused forward + single-kernel
+    backward take 72 us per BERT-base layer against 103 us for GEMM + softmax + GEMM (tf32; 57 vs 76 us in bf16).
+    For longer sequences the two-kernel backward is still slower than the unfused GEMMs, so it is opt-in there
+    (B200_FUSED_ATTN=1; it saves the 2 * B * heads * L * L activation tensors).  B200_FUSED_ATTN=0 disables it."""
+    import os
+    flag = os.environ.get("B200_FUSED_ATTN", "")
+    if dh != 64 or flag == "0":
+        return False
+    return L <= 128 or flag == "1"
+
+
+def _attention_unfused(qkv, nctx, attn_mask, B, L, Lp, H, heads, dh, sid, p_attn):
+    """Score GEMM -> softmax (+mask, +dropout) -> context GEMM; returns (ctx, P, Pdrop)."""
+    dev, dt = qkv.device, qkv.dtype
     S = torch.empty((B, heads, L, Lp), dtype=dt, device=dev)
     if _fused_softmax(L):
         # softmax (+ mask, + dropout copy) runs in the epilogue of the score GEMM: the scores never reach memory
@@ -146,6 +156,21 @@ def _layer_forward(x, nctx, lp, attn_mask, B, L, sid, p_attn, p_hid):
     ctxv = torch.empty((B * L, H), dtype=dt, device=dev)
     bgemm(Pd, qkv, ctxv, M=L, N=dh, K=L, lda=Lp, ldb=3 * H, ldd=H, a_mn=False, b_mn=True, batch0=heads, batch1=B,
           sa=(L * Lp, heads * L * Lp), sb=(dh, L * 3 * H), sd=(dh, L * H), b_off=2 * H)
+    return ctxv, S, Pd
+
+
+def _layer_forward(x, nctx, lp, attn_mask, B, L, sid, p_attn, p_hid):
+    """Forward kernels of one encoder layer; returns (output, tensors backward needs)."""
+    H = x.shape[1]
+    heads, dh = lp.heads, lp.dh
+    Lp = _pad8(L)
+    dev, dt = x.device, x.dtype
+    qkv = gemm(x, lp.Wqkv, bias=lp.bqkv)                                                    # [M, 3H]
+    if _fused_attention(L, dh):
+        ctxv, lse = K.attn_fwd(qkv, attn_mask, B, heads, L, 1.0 / math.sqrt(dh), p_attn, nctx.seed, sid + 1, Lp=Lp)
+        S, Pd = lse, None               # backward recomputes the probabilities from the saved log-sum-exp
+    else:
+        ctxv, S, Pd = _attention_unfused(qkv, nctx, attn_mask, B, L, Lp, H, heads, dh, sid, p_attn)
     z1 = gemm(ctxv, lp.Wo)
     y1, mean1, rstd1 = K.ln_fwd(z1, lp.g1, lp.be1, bias=lp.bo, residual=x, eps=lp.eps, p_pre=p_hid, seed=nctx.seed,
                                 stream_pre=sid + 2)
@@ -155,6 +180,33 @@ def _layer_forward(x, nctx, lp, attn_mask, B, L, sid, p_attn, p_hid):
     y2, mean2, rstd2 = K.ln_fwd(z2, lp.g2, lp.be2, bias=lp.b2, residual=y1, eps=lp.eps, p_pre=p_hid, seed=nctx.seed,
                                 stream_pre=sid + 3)
     return y2, (qkv, S, Pd, ctxv, z1, y1, mean1, rstd1, u, a, z2, mean2, rstd2)
+
+
+def _attention_unfused_bwd(qkv, P, Pd, dctx, nctx, B, L, Lp, H, heads, dh, sid, p_attn):
+    """dqkv of the unfused attention: four batched GEMMs around the softmax backward kernel."""
+    dt, dev = qkv.dtype, qkv.device
+    scale = 1.0 / math.sqrt(dh)
+    sS = (L * Lp, heads * L * Lp)
+    sQ = (dh, L * 3 * H)
+    sC = (dh, L * H)
+    dP = torch.empty((B, heads, L, Lp), dtype=dt, device=dev)
+    fused = _fused_softmax(L)
+    if fused:     # dS = P * (dPe - rowsum(P*dPe)) computed in the epilogue of the dP GEMM
+        bgemm(dctx, qkv, dP, M=L, N=L, K=dh, lda=H, ldb=3 * H, ldd=Lp, a_mn=False, b_mn=False, batch0=heads, batch1=B,
+              sa=sC, sb=sQ, sd=sS, b_off=2 * H, epi_mode=2, aux=P, p_drop=p_attn, seed=nctx.seed, stream_id=sid + 1)
+    else:
+        bgemm(dctx, qkv, dP, M=L, N=L, K=dh, lda=H, ldb=3 * H, ldd=Lp, a_mn=False, b_mn=False, batch0=heads, batch1=B,
+              sa=sC, sb=sQ, sd=sS, b_off=2 * H)                                               # dP = dctx V^T
+    dqkv = torch.empty((B * L, 3 * H), dtype=dt, device=dev)
+    bgemm(Pd, dctx, dqkv, M=L, N=dh, K=L, lda=Lp, ldb=H, ldd=3 * H, a_mn=True, b_mn=True, batch0=heads, batch1=B,
+          sa=sS, sb=sC, sd=sQ, d_off=2 * H)                                                   # dV = Pd^T dctx
+    if not fused:
+        K.softmax_bwd_(P, dP, B, heads, L, Lp, p_attn, nctx.seed, sid + 1)                    # dP <- dS
+    bgemm(dP, qkv, dqkv, M=L, N=dh, K=L, lda=Lp, ldb=3 * H, ldd=3 * H, a_mn=False, b_mn=True, batch0=heads, batch1=B,
+          sa=sS, sb=sQ, sd=sQ, b_off=H, alpha=scale)                                          # dQ = dS K / sqrt(d)
+    bgemm(dP, qkv, dqkv, M=L, N=dh, K=L, lda=Lp, ldb=3 * H, ldd=3 * H, a_mn=True, b_mn=True, batch0=heads, batch1=B,
+          sa=sS, sb=sQ, sd=sQ, d_off=H, alpha=scale)                                          # dK = dS^T Q / sqrt(d)
+    return dqkv
 
 
 class BertLayerFn(torch.autograd.Function):
@@ -214,26 +266,10 @@ class BertLayerFn(torch.autograd.Function):
 
         # ---- attention core -------------------------------------------------------------------------------
         scale = 1.0 / math.sqrt(dh)
-        sS = (L * Lp, heads * L * Lp)
-        sQ = (dh, L * 3 * H)
-        sC = (dh, L * H)
-        dP = torch.empty((B, heads, L, Lp), dtype=dt, device=dev)
-        fused = _fused_softmax(L)
-        if fused:     # dS = P * (dPe - rowsum(P*dPe)) computed in the epilogue of the dP GEMM
-            bgemm(dctx, qkv, dP, M=L, N=L, K=dh, lda=H, ldb=3 * H, ldd=Lp, a_mn=False, b_mn=False, batch0=heads, batch1=B,
-                  sa=sC, sb=sQ, sd=sS, b_off=2 * H, epi_mode=2, aux=P, p_drop=p_attn, seed=nctx.seed, stream_id=sid + 1)
+        if Pd is None:      # fused path: P holds the log-sum-exp saved by attn_fwd
+            dqkv = K.attn_bwd(qkv, ctxv, dctx, P, ctx.attn_mask, B, heads, L, scale, p_attn, nctx.seed, sid + 1, Lp=Lp)
         else:
-            bgemm(dctx, qkv, dP, M=L, N=L, K=dh, lda=H, ldb=3 * H, ldd=Lp, a_mn=False, b_mn=False, batch0=heads, batch1=B,
-                  sa=sC, sb=sQ, sd=sS, b_off=2 * H)                                               # dP = dctx V^T
-        dqkv = torch.empty((B * L, 3 * H), dtype=dt, device=dev)
-        bgemm(Pd, dctx, dqkv, M=L, N=dh, K=L, lda=Lp, ldb=H, ldd=3 * H, a_mn=True, b_mn=True, batch0=heads, batch1=B,
-              sa=sS, sb=sC, sd=sQ, d_off=2 * H)                                                   # dV = Pd^T dctx
-        if not fused:
-            K.softmax_bwd_(P, dP, B, heads, L, Lp, p_attn, nctx.seed, sid + 1)                    # dP <- dS
-        bgemm(dP, qkv, dqkv, M=L, N=dh, K=L, lda=Lp, ldb=3 * H, ldd=3 * H, a_mn=False, b_mn=True, batch0=heads, batch1=B,
-              sa=sS, sb=sQ, sd=sQ, b_off=H, alpha=scale)                                          # dQ = dS K / sqrt(d)
-        bgemm(dP, qkv, dqkv, M=L, N=dh, K=L, lda=Lp, ldb=3 * H, ldd=3 * H, a_mn=True, b_mn=True, batch0=heads, batch1=B,
-              sa=sS, sb=sQ, sd=sQ, d_off=H, alpha=scale)                                          # dK = dS^T Q / sqrt(d)
+            dqkv = _attention_unfused_bwd(qkv, P, Pd, dctx, nctx, B, L, Lp, H, heads, dh, sid, p_attn)
 
         # ---- QKV projection -------------------------------------------------------------------------------
         K.colsum_(dqkv, lp.gbqkv, ws)

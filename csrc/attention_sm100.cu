@@ -520,15 +520,16 @@ static int attn_fwd_impl(const b200_attn_args* g, cudaStream_t st) {
   std::call_once(once, [] {
     cudaFuncSetAttribute(attn_fwd_wide_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, fwd_smem<T>());
   });
-  CUtensorMap tq, tv;
+  CUtensorMap tq, tv, to;
   if (int e = head_map<T>(&tq, g->qkv, g->B, 3 * g->heads, g->L, g->ld_qkv, false)) return e;
   if (int e = head_map<T>(&tv, g->qkv, g->B, 3 * g->heads, g->L, g->ld_qkv, true)) return e;
+  if (int e = head_map<T>(&to, g->out, g->B, g->heads, g->L, g->ld_out, false)) return e;
   AttnArgs a{};
   a.B = g->B; a.heads = g->heads; a.L = g->L; a.Lp = g->Lp;
   a.scale = g->scale; a.p_drop = g->p_drop; a.mask = g->attn_mask; a.seed_dev = g->seed_dev; a.stream_id = g->stream_id;
   a.out = g->out; a.ld_out = g->ld_out; a.lse = g->lse;
   dim3 grid((g->L + 127) / 128, g->heads, g->B);
-  attn_fwd_wide_kernel<T><<<grid, kWideThreads, fwd_smem<T>(), st>>>(tq, tv, a);
+  attn_fwd_wide_kernel<T><<<grid, kWideThreads, fwd_smem<T>(), st>>>(tq, tv, to, a);
   B200_LAUNCHED("attn_fwd_wide_kernel");
   return 0;
 }

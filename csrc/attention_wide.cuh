@@ -59,167 +59,6 @@ __device__ __forceinline__ void store_row16(T* p, const float (&v)[16]) {
   for (int i = 0; i < 4; ++i) store4<T>(p + i * 4, f4{v[i * 4], v[i * 4 + 1], v[i * 4 + 2], v[i * 4 + 3]});
 }
 
-// =====================================================================================================
-// forward, 512 threads.  grid = (q blocks, heads, B)
-// =====================================================================================================
-// smem: Q | K | V(mn) | P[128 x 128] | mask[128] | red[4][128] | barriers.   TMEM: S [0,128), O_blk [128,192)
-template <typename T>
-__global__ void __launch_bounds__(kWideThreads, 1)
-attn_fwd_wide_kernel(const __grid_constant__ CUtensorMap tmQK, const __grid_constant__ CUtensorMap tmVmn,
-                     const AttnArgs a) {
-  using C = AttCfg<T>;
-  constexpr int OPB = C::ATOMS * kTile;
-  extern __shared__ __align__(1024) uint8_t smem_raw[];
-  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
-  uint8_t* sQ = smem;
-  uint8_t* sK = smem + OPB;
-  uint8_t* sV = smem + 2 * OPB;
-  uint8_t* sP = smem + 3 * OPB;                                   // 2*OPB bytes
-  float* sMask = reinterpret_cast<float*>(smem + 5 * OPB);
-  float* sRed = sMask + 128;                                      // [4][128]
-  uint64_t* bars = reinterpret_cast<uint64_t*>(sRed + 512);
-  uint64_t *bar_q = bars, *bar_kv = bars + 1, *bar_s = bars + 2, *bar_pv = bars + 3;
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 4);
-
-  const int t = threadIdx.x, warp = t >> 5, lane = t & 31;
-  const int lq = warp & 3, cq = warp >> 2;
-  const int row = lq * 32 + lane;
-  const int h = blockIdx.y, b = blockIdx.z;
-  const int q0 = blockIdx.x * 128;
-  const int qrow = q0 + row;
-  const bool qlive = qrow < a.L;
-
-  if (t == 0) {
-    tma_prefetch_desc(&tmQK);
-    tma_prefetch_desc(&tmVmn);
-    mbar_init(bar_q, 1); mbar_init(bar_kv, 1); mbar_init(bar_s, 1); mbar_init(bar_pv, 1);
-    fence_barrier_init();
-  }
-  if (warp == 0) tmem_alloc<256>(tmem_slot);
-  tcgen05_fence_before();
-  __syncthreads();
-  tcgen05_fence_after();
-  const uint32_t tmem = *tmem_slot;
-  const uint32_t tS = tmem + ((uint32_t)(lq * 32) << 16) + cq * 32;
-  const uint32_t tO = tmem + ((uint32_t)(lq * 32) << 16) + 128 + cq * 16;
-
-  constexpr uint32_t IDESC_S = make_idesc(C::FMT, false, false, 128, 128);
-  constexpr uint32_t IDESC_O = make_idesc(C::FMT, false, true, 128, 64);
-
-  if (t == 0) {
-    mbar_arrive_expect_tx(bar_q, OPB);
-    load_tile<T>(sQ, &tmQK, bar_q, q0, h, b);
-  }
-
-  const Philox ph(a.seed_dev ? *a.seed_dev : 0ull);
-  const uint32_t thr = dropout_threshold(a.p_drop);
-  const float ik = a.p_drop > 0.f ? 1.f / (1.f - a.p_drop) : 1.f;
-  const long long rowg = (((long long)b * a.heads + h) * a.L + qrow) * a.Lp;
-
-  float o_acc[16];
-#pragma unroll
-  for (int i = 0; i < 16; ++i) o_acc[i] = 0.f;
-  float m_run = -3.0e38f, l_part = 0.f;
-
-  const int nkv = (a.L + 127) / 128;
-  for (int j = 0; j < nkv; ++j) {
-    const int k0 = j * 128;
-    if (t == 0) {
-      mbar_arrive_expect_tx(bar_kv, 2 * OPB);
-      load_tile<T>(sK, &tmQK, bar_kv, k0, a.heads + h, b);
-      load_tile<T>(sV, &tmVmn, bar_kv, k0, 2 * a.heads + h, b);
-    }
-    if (t < 128) {
-      const int k = k0 + t;
-      float mv = -3.0e38f;
-      if (k < a.L) mv = a.mask ? (1.f - (float)a.mask[(long long)b * a.L + k]) * -10000.f : 0.f;
-      sMask[t] = mv;
-    }
-    if (t == 0) {
-      if (j == 0) mbar_wait(bar_q, 0);
-      mbar_wait(bar_kv, j & 1);
-      tcgen05_fence_after();
-      const uint32_t qa = smem_u32(sQ), ka = smem_u32(sK);
-#pragma unroll
-      for (int s = 0; s < C::STEPS; ++s)
-        tcgen05_mma_ss<C::KIND>(tmem, desc_k<T>(qa, s), desc_k<T>(ka, s), IDESC_S, s > 0 ? 1u : 0u);
-      tcgen05_commit(bar_s);
-    }
-    __syncthreads();
-    mbar_wait(bar_s, j & 1);
-    tcgen05_fence_after();
-
-    float p[32];
-    ld32(tS, p);
-    float m_loc = -3.0e38f;
-#pragma unroll
-    for (int i = 0; i < 32; ++i) {
-      const float mv = sMask[cq * 32 + i];
-      p[i] = mv > -1.0e38f ? p[i] * a.scale + mv : -3.0e38f;
-      m_loc = fmaxf(m_loc, p[i]);
-    }
-    sRed[cq * 128 + row] = m_loc;
-    __syncthreads();
-    const float m_new = fmaxf(fmaxf(m_run, fmaxf(sRed[row], sRed[128 + row])), fmaxf(sRed[256 + row], sRed[384 + row]));
-    const float alpha = __expf(m_run - m_new);
-    float l_loc = 0.f;
-#pragma unroll
-    for (int i = 0; i < 32; ++i) {
-      p[i] = p[i] > -1.0e38f ? __expf(p[i] - m_new) : 0.f;
-      l_loc += p[i];
-    }
-    l_part = l_part * alpha + l_loc;
-    m_run = m_new;
-    if (a.p_drop > 0.f) {
-#pragma unroll
-      for (int i = 0; i < 32; i += 4) {
-        const f4 d = dropout_scale4(ph, (unsigned long long)(rowg + k0 + cq * 32 + i), a.stream_id, thr, ik);
-        p[i] *= d.x; p[i + 1] *= d.y; p[i + 2] *= d.z; p[i + 3] *= d.w;
-      }
-    }
-    store_slice_row<T>(sP, row, cq, p);
-    fence_proxy_async_smem();
-    tcgen05_fence_before();
-    __syncthreads();
-    if (t == 0) {
-      tcgen05_fence_after();
-      const uint32_t pa = smem_u32(sP), va = smem_u32(sV);
-#pragma unroll
-      for (int s = 0; s < 2 * C::STEPS; ++s)
-        tcgen05_mma_ss<C::KIND>(tmem + 128, desc_k<T>(pa, s), desc_mn<T>(va, 0, s), IDESC_O, s > 0 ? 1u : 0u);
-      tcgen05_commit(bar_pv);
-    }
-    mbar_wait(bar_pv, j & 1);
-    tcgen05_fence_after();
-    {
-      float v[16];
-      ld16(tO, v);
-#pragma unroll
-      for (int i = 0; i < 16; ++i) o_acc[i] = o_acc[i] * alpha + v[i];
-    }
-    tcgen05_fence_before();
-    __syncthreads();           // sRed, sMask, sK/sV/sP and TMEM are free for the next block
-  }
-
-  sRed[cq * 128 + row] = l_part;
-  __syncthreads();
-  const float l_run = sRed[row] + sRed[128 + row] + sRed[256 + row] + sRed[384 + row];
-  if (qlive) {
-    const float inv = l_run > 0.f ? 1.f / l_run : 0.f;
-#pragma unroll
-    for (int i = 0; i < 16; ++i) o_acc[i] *= inv;
-    T* dst = reinterpret_cast<T*>(a.out) + ((long long)b * a.L + qrow) * a.ld_out + h * 64 + cq * 16;
-    store_row16<T>(dst, o_acc);
-    if (a.lse && cq == 0) a.lse[((long long)b * a.heads + h) * a.L + qrow] = m_run + logf(fmaxf(l_run, 1e-37f));
-  }
-  tcgen05_fence_before();
-  __syncthreads();
-  if (warp == 0) {
-    tcgen05_fence_after();
-    tmem_dealloc<256>(tmem);
-  }
-}
-
 // ---- generator forms of the slice stores: `get(i)` yields value i of the thread's 32, so callers need not
 // materialise a second 32-register array --------------------------------------------------------------------------
 template <typename T, typename F>
@@ -284,6 +123,172 @@ __device__ __forceinline__ void store_tile(const CUtensorMap* tm, const uint8_t*
   using C = AttCfg<T>;
 #pragma unroll
   for (int a = 0; a < C::ATOMS; ++a) tma_store_4d(tm, tile + a * kTile, a * C::EPA, r0, h, b);
+}
+
+// =====================================================================================================
+// forward, 512 threads.  grid = (q blocks, heads, B)
+// =====================================================================================================
+// smem: Q | K | V(mn) | P[128 x 128] | mask[128] | red[4][128] | barriers.   TMEM: S [0,128), O_blk [128,192)
+template <typename T>
+__global__ void __launch_bounds__(kWideThreads, 1)
+attn_fwd_wide_kernel(const __grid_constant__ CUtensorMap tmQK, const __grid_constant__ CUtensorMap tmVmn,
+                     const __grid_constant__ CUtensorMap tmOut, const AttnArgs a) {
+  using C = AttCfg<T>;
+  constexpr int OPB = C::ATOMS * kTile;
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* sQ = smem;
+  uint8_t* sK = smem + OPB;
+  uint8_t* sV = smem + 2 * OPB;
+  uint8_t* sP = smem + 3 * OPB;                                   // 2*OPB bytes
+  float* sMask = reinterpret_cast<float*>(smem + 5 * OPB);
+  float* sRed = sMask + 128;                                      // [4][128]
+  uint64_t* bars = reinterpret_cast<uint64_t*>(sRed + 512);
+  uint64_t *bar_q = bars, *bar_k = bars + 1, *bar_v = bars + 2, *bar_s = bars + 3, *bar_pv = bars + 4;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 5);
+
+  const int t = threadIdx.x, warp = t >> 5, lane = t & 31;
+  const int lq = warp & 3, cq = warp >> 2;
+  const int row = lq * 32 + lane;
+  const int h = blockIdx.y, b = blockIdx.z;
+  const int q0 = blockIdx.x * 128;
+  const int qrow = q0 + row;
+  const bool qlive = qrow < a.L;
+
+  if (t == 0) {
+    tma_prefetch_desc(&tmQK);
+    tma_prefetch_desc(&tmVmn);
+    tma_prefetch_desc(&tmOut);
+    mbar_init(bar_q, 1); mbar_init(bar_k, 1); mbar_init(bar_v, 1); mbar_init(bar_s, 1); mbar_init(bar_pv, 1);
+    fence_barrier_init();
+    mbar_arrive_expect_tx(bar_q, OPB);
+    load_tile<T>(sQ, &tmQK, bar_q, q0, h, b);
+  }
+  if (warp == 1) tmem_alloc<256>(tmem_slot);
+  tcgen05_fence_before();
+  __syncthreads();
+  tcgen05_fence_after();
+  const uint32_t tmem = *tmem_slot;
+  const uint32_t tS = tmem + ((uint32_t)(lq * 32) << 16) + cq * 32;
+  const uint32_t tO = tmem + ((uint32_t)(lq * 32) << 16) + 128 + cq * 16;
+
+  constexpr uint32_t IDESC_S = make_idesc(C::FMT, false, false, 128, 128);
+  constexpr uint32_t IDESC_O = make_idesc(C::FMT, false, true, 128, 64);
+
+  const Philox ph(a.seed_dev ? *a.seed_dev : 0ull);
+  const uint32_t thr = dropout_threshold(a.p_drop);
+  const float ik = a.p_drop > 0.f ? 1.f / (1.f - a.p_drop) : 1.f;
+  const long long rowg = (((long long)b * a.heads + h) * a.L + qrow) * a.Lp;
+
+  float o_acc[16];
+#pragma unroll
+  for (int i = 0; i < 16; ++i) o_acc[i] = 0.f;
+  float m_run = -3.0e38f, l_part = 0.f;
+
+  const int nkv = (a.L + 127) / 128;
+  for (int j = 0; j < nkv; ++j) {
+    const int k0 = j * 128;
+    if (t == 0) {
+      mbar_arrive_expect_tx(bar_k, OPB);
+      load_tile<T>(sK, &tmQK, bar_k, k0, a.heads + h, b);
+      mbar_arrive_expect_tx(bar_v, OPB);
+      load_tile<T>(sV, &tmVmn, bar_v, k0, 2 * a.heads + h, b);
+    }
+    if (t >= 128 && t < 256) {
+      const int k = k0 + t - 128;
+      float mv = -3.0e38f;
+      if (k < a.L) mv = a.mask ? (1.f - (float)a.mask[(long long)b * a.L + k]) * -10000.f : 0.f;
+      sMask[t - 128] = mv;
+    }
+    if (t == 0) {
+      if (j == 0) mbar_wait(bar_q, 0);
+      mbar_wait(bar_k, j & 1);
+      tcgen05_fence_after();
+      const uint32_t qa = smem_u32(sQ), ka = smem_u32(sK);
+#pragma unroll
+      for (int s = 0; s < C::STEPS; ++s)
+        tcgen05_mma_ss<C::KIND>(tmem, desc_k<T>(qa, s), desc_k<T>(ka, s), IDESC_S, s > 0 ? 1u : 0u);
+      tcgen05_commit(bar_s);
+    }
+    __syncthreads();
+    mbar_wait(bar_s, j & 1);
+    tcgen05_fence_after();
+
+    float p[32];
+    ld32(tS, p);
+    float m_loc = -3.0e38f;
+#pragma unroll
+    for (int i = 0; i < 32; ++i) {
+      const float mv = sMask[cq * 32 + i];
+      p[i] = mv > -1.0e38f ? p[i] * a.scale + mv : -3.0e38f;
+      m_loc = fmaxf(m_loc, p[i]);
+    }
+    sRed[cq * 128 + row] = m_loc;
+    __syncthreads();
+    const float m_new = fmaxf(fmaxf(m_run, fmaxf(sRed[row], sRed[128 + row])), fmaxf(sRed[256 + row], sRed[384 + row]));
+    const float alpha = __expf(m_run - m_new);
+    float l_loc = 0.f;
+#pragma unroll
+    for (int i = 0; i < 32; ++i) {
+      p[i] = p[i] > -1.0e38f ? __expf(p[i] - m_new) : 0.f;
+      l_loc += p[i];
+    }
+    l_part = l_part * alpha + l_loc;
+    m_run = m_new;
+    if (a.p_drop > 0.f) {
+#pragma unroll
+      for (int i = 0; i < 32; i += 4) {
+        const f4 d = dropout_scale4(ph, (unsigned long long)(rowg + k0 + cq * 32 + i), a.stream_id, thr, ik);
+        p[i] *= d.x; p[i + 1] *= d.y; p[i + 2] *= d.z; p[i + 3] *= d.w;
+      }
+    }
+    store_slice_row<T>(sP, row, cq, p);
+    fence_proxy_async_smem();
+    tcgen05_fence_before();
+    __syncthreads();
+    if (t == 0) {
+      mbar_wait(bar_v, j & 1);
+      tcgen05_fence_after();
+      const uint32_t pa = smem_u32(sP), va = smem_u32(sV);
+#pragma unroll
+      for (int s = 0; s < 2 * C::STEPS; ++s)
+        tcgen05_mma_ss<C::KIND>(tmem + 128, desc_k<T>(pa, s), desc_mn<T>(va, 0, s), IDESC_O, s > 0 ? 1u : 0u);
+      tcgen05_commit(bar_pv);
+    }
+    mbar_wait(bar_pv, j & 1);
+    tcgen05_fence_after();
+    {
+      float v[16];
+      ld16(tO, v);
+#pragma unroll
+      for (int i = 0; i < 16; ++i) o_acc[i] = o_acc[i] * alpha + v[i];
+    }
+    tcgen05_fence_before();
+    __syncthreads();           // sRed, sMask, sK/sV/sP and TMEM are free for the next block
+  }
+
+  sRed[cq * 128 + row] = l_part;
+  __syncthreads();
+  const float l_run = sRed[row] + sRed[128 + row] + sRed[256 + row] + sRed[384 + row];
+  {
+    const float inv = l_run > 0.f ? 1.f / l_run : 0.f;
+#pragma unroll
+    for (int i = 0; i < 16; ++i) o_acc[i] *= inv;
+    stage_row16<T>(sP, row, cq, o_acc);                    // sP is idle: the last P V product has completed
+    if (qlive && a.lse && cq == 0) a.lse[((long long)b * a.heads + h) * a.L + qrow] = m_run + __logf(fmaxf(l_run, 1e-37f));
+  }
+  fence_proxy_async_smem();
+  tcgen05_fence_before();
+  __syncthreads();
+  if (t == 0) {
+    store_tile<T>(&tmOut, sP, q0, h, b);                   // rows past L are clipped by the tensor map
+    tma_store_commit();
+    tma_store_wait_read<0>();
+  }
+  if (warp == 1) {
+    tcgen05_fence_after();
+    tmem_dealloc<256>(tmem);
+  }
 }
 
 // =====================================================================================================

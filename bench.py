@@ -32,6 +32,13 @@ import time
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
+def _metric_name(model: str, seq_len: int) -> str:
+    """BASELINE.json's headline is BERT-base phase 1 (seq 128); the other configs it lists get their own label."""
+    pretty = {"bert-base": "BERT-base", "bert-large": "BERT-large"}.get(model, model)
+    phase = {128: "phase-1 ", 512: "phase-2 "}.get(seq_len, "")
+    return f"{pretty} {phase}pre-training throughput (seq {seq_len})"
+
+
 PUBLISHED_SEQ_PER_SEC_PER_GPU = 12.3   # BASELINE.md §A: 49.2 seq/s on 4 GPUs (README.md:65 of the reference)
 
 
@@ -236,7 +243,7 @@ def run_ours(a):
         gb = a.batch * world
         value = gb * a.steps / (dev_ms / 1e3)
         out = {
-            "metric": "BERT-base phase-1 pre-training throughput (seq 128)" if a.model == "bert-base" else a.model + " throughput",
+            "metric": _metric_name(a.model, a.seq_len),
             "value": round(value, 2), "unit": "sequences/s", "n_gpus": world, "steps": a.steps, "warmup": a.warmup,
             "ms_per_step": round(dev_ms / a.steps, 4), "higher_is_better": True, "scaling": "weak",
             "vs_baseline": round(value / (PUBLISHED_SEQ_PER_SEC_PER_GPU * world), 2), "dtype": a.precision, "data": "synthetic",

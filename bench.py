@@ -42,7 +42,7 @@ def _metric_name(model: str, seq_len: int) -> str:
 PUBLISHED_SEQ_PER_SEC_PER_GPU = 12.3   # 49.2 seq/s on 4 GPUs (README.md:65 of the reference)
 
 
-def parse():
+def parse(argv=None):
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=20)
@@ -54,8 +54,10 @@ def parse():
     ap.add_argument("--model", default="bert-base", choices=["bert-base", "bert-large", "bert-tiny"])
     ap.add_argument("--comm", default="auto")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-device-batch", action="store_true",
+                    help="ship five int64 tensors per batch instead of one packed int32 matrix assembled on the GPU")
     ap.add_argument("--no-graph", action="store_true", help="issue every kernel from Python instead of replaying a CUDA graph")
-    return ap.parse_args()
+    return ap.parse_args(argv)
 
 
 MODELS = {
@@ -66,32 +68,82 @@ MODELS = {
 
 
 class ClockSampler:
-    """Samples SM clock / throttle reasons with nvidia-smi every 200 ms while the timed region runs."""
+    """Samples the SM clock and the throttle reasons every 50 ms while the timed regions run.
 
-    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
-         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+    NVML in-process (nvidia_ml_py): a query costs microseconds.  Spawning ``nvidia-smi -lms`` instead initialises a
+    second driver client in the middle of the measurement, which was measured to stall one training step by ~19 ms
+    (profiles/README.md §8); it is only the fallback when NVML cannot be loaded."""
+
+    REASONS = (("hw_slowdown", 0x8), ("hw_thermal_slowdown", 0x40), ("sw_thermal_slowdown", 0x20), ("sw_power_cap", 0x4))
 
     def __init__(self, gpu_index: int):
         self.gpu = gpu_index
-        self.proc = None
-        self.lines = []
+        self.samples, self.reasons = [], set()
+        self.max_mhz = None
+        self._stop = threading.Event()
+        self._thread = None
+        self._nvml = None
+        self._handle = None
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            handle = None
+            try:
+                import torch
+                uuid = str(torch.cuda.get_device_properties(gpu_index).uuid)
+                handle = pynvml.nvmlDeviceGetHandleByUUID(("GPU-" + uuid) if not uuid.startswith("GPU-") else uuid)
+            except Exception:
+                handle = pynvml.nvmlDeviceGetHandleByIndex(gpu_index)
+            self._nvml, self._handle = pynvml, handle
+            self.max_mhz = float(pynvml.nvmlDeviceGetMaxClockInfo(handle, pynvml.NVML_CLOCK_SM))
+        except Exception:
+            self._nvml = None
+
+    def _poll(self):
+        nv, h = self._nvml, self._handle
+        while not self._stop.is_set():
+            try:
+                self.samples.append(float(nv.nvmlDeviceGetClockInfo(h, nv.NVML_CLOCK_SM)))
+                mask = int(nv.nvmlDeviceGetCurrentClocksEventReasons(h))
+                for name, bit in self.REASONS:
+                    if mask & bit:
+                        self.reasons.add(name)
+            except Exception:
+                pass
+            self._stop.wait(0.05)
 
     def start(self):
+        if self._nvml is None:
+            return self._start_smi()
+        self._thread = threading.Thread(target=self._poll, daemon=True, name="clock-sampler")
+        self._thread.start()
+
+    def stop(self):
+        if self._nvml is None:
+            return self._stop_smi()
+        self._stop.set()
+        self._thread.join(timeout=2)
+        sm = sorted(self.samples)
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons),
+                "samples": len(sm), "source": "nvml"}
+
+    # ---- fallback: one long-running nvidia-smi -------------------------------------------------------------------
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def _start_smi(self):
+        self.lines = []
         try:
             self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.gpu), "--query-gpu=" + self.Q,
                                           "--format=csv,noheader,nounits", "-lms", "200"], stdout=subprocess.PIPE,
                                          stderr=subprocess.DEVNULL, text=True)
-            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t = threading.Thread(target=lambda: [self.lines.append(ln.strip()) for ln in self.proc.stdout], daemon=True)
             self.t.start()
         except Exception:
             self.proc = None
 
-    def _read(self):
-        for line in self.proc.stdout:
-            self.lines.append(line.strip())
-
-    def stop(self):
-        if self.proc is None:
+    def _stop_smi(self):
+        if getattr(self, "proc", None) is None:
             return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
         self.proc.terminate()
         try:
@@ -112,7 +164,7 @@ class ClockSampler:
                     reasons.add(name)
         sm.sort()
         return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": max(mx) if mx else None,
-                "reasons": sorted(reasons), "samples": len(sm)}
+                "reasons": sorted(reasons), "samples": len(sm), "source": "nvidia-smi"}
 
 
 def _dist_env():
@@ -132,6 +184,8 @@ def make_args(a, data_dir, cfg_path, vocab_path, rank, local, world):
             "--max-predictions-per-seq", "20" if a.seq_len <= 128 else "80", "--disable-validation"]
     if not a.no_graph:
         argv.append("--cuda-graph")
+    if not a.no_device_batch:
+        argv.append("--device-batch-assembly")
     args = options.parse_training_args(argv)
     args.distributed_rank = rank
     args.device_id = local
@@ -177,18 +231,25 @@ def run_ours(a):
                 dist.barrier()
                 torch.cuda.synchronize()
 
+        def stage(sample):
+            """Device-resident copy of a batch for the device-timed region (packed batches are assembled once)."""
+            from hetseq_9cme_b200.data.packed import PackedBertBatch
+            if isinstance(sample, PackedBertBatch):           # raw matrix resident on the device, meta stays on the host
+                return PackedBertBatch([sample[0].cuda(non_blocking=True), sample[1]])
+            return [t.cuda(non_blocking=True) for t in sample]
+
         # ---- warm-up through the public path ------------------------------------------------------------
         staged = []
         for _ in range(a.warmup):
             sample = next(itr)
             controller.train_step([sample])
-            staged.append([t.cuda(non_blocking=True) for t in sample])
+            staged.append(stage(sample))
         controller.flush_stats()
         sync_all()
 
         # ---- device-timed region: inputs resident ---------------------------------------------------------
         while len(staged) < 4:
-            staged.append([t.cuda() for t in next(itr)])
+            staged.append(stage(next(itr)))
         sampler = ClockSampler(local)
         sampler.start()
         native.reset_launch_count()
@@ -213,14 +274,34 @@ def run_ours(a):
             sync_all()
             h2d = d2h = 0
             t0 = time.perf_counter()
+            marks = [t0]
+            fetch_ms = []
+            import gc
+            gc_log, gc_t = [], [0.0]
+
+            def _gc_cb(phase, info):
+                if phase == "start":
+                    gc_t[0] = time.perf_counter()
+                else:
+                    gc_log.append((info.get("generation"), round((time.perf_counter() - gc_t[0]) * 1e3, 3)))
+            gc.callbacks.append(_gc_cb)
             for s in range(a.steps):
                 sample = next(itr)
-                h2d += sum(t.numel() * t.element_size() for t in sample)
+                fetch_ms.append((time.perf_counter() - marks[-1]) * 1e3)
+                h2d += sum(t.numel() * t.element_size() for t in (sample[:1] if args.device_batch_assembly else sample))
                 out = controller.train_step([sample])
                 d2h += 8 * 8
+                marks.append(time.perf_counter())
             controller.flush_stats()           # host has read every step's loss / gnorm
             sync_all()
             e2e_ms = (time.perf_counter() - t0) * 1e3
+            gc.callbacks.remove(_gc_cb)
+            per = sorted((b - a_) * 1e3 for a_, b in zip(marks, marks[1:]))
+            raw_per = [(b - a_) * 1e3 for a_, b in zip(marks, marks[1:])]
+            e2e_host = {"first_ms": round((marks[1] - marks[0]) * 1e3, 3), "median_ms": round(per[len(per) // 2], 3),
+                        "max_ms": round(per[-1], 3), "max_at": raw_per.index(max(raw_per)), "max_fetch_ms": round(max(fetch_ms), 3),
+                        "gc_pauses_over_1ms": [g for g in gc_log if g[1] > 1.0],
+                        "drain_ms": round(e2e_ms - (marks[-1] - t0) * 1e3, 3)}
         clocks = sampler.stop()
 
         # ---- exposed all-reduce time: a few eagerly issued steps with timing events around the post-backward wait ----
@@ -261,7 +342,7 @@ def run_ours(a):
         if not a.no_e2e:
             out["e2e"] = {"value": round(gb * a.steps / (e2e_ms / 1e3), 2), "unit": "sequences/s",
                           "ms_per_step": round(e2e_ms / a.steps, 4), "h2d_bytes_per_step": int(h2d / a.steps),
-                          "d2h_bytes_per_step": int(d2h / a.steps)}
+                          "d2h_bytes_per_step": int(d2h / a.steps), "host_step": e2e_host}
         if rank == 0:
             print(json.dumps(out), flush=True)
         if world > 1:

@@ -103,6 +103,7 @@ class Controller:
         # CUDA-graph replay of the fixed-shape step (--cuda-graph)
         self._graph_enabled = bool(getattr(args, "cuda_graph", False)) and self.cuda
         self._graph = None
+        self._g_raw = None
         self._graph_sig = None
         self._graph_seen = 0
         self.init_meters(args)
@@ -285,9 +286,31 @@ class Controller:
     def _prepare_sample(self, sample):
         if utils.sample_is_empty(sample):
             return None
+        from .data.packed import PackedBertBatch
+        if isinstance(sample, PackedBertBatch):          # --device-batch-assembly: one H2D copy + one kernel
+            return self._batch_assembler().assemble(sample)
         if self.cuda:
             sample = utils.move_to_cuda(sample, self.device, non_blocking=True)
         return sample
+
+    def _settle_gc(self, again: bool = False):
+        """Move everything built so far (model, arena views, datasets: ~170k objects for BERT-base) into the garbage
+        collector's permanent generation.  A full collection over them takes 20-80 ms of host time, and with the
+        GPU at most one step behind the host that is a bubble on the device: measured as one 27 ms step in every
+        ~30 on B200 (profiles/README.md §8).  Frozen objects are skipped by later collections, which then only scan
+        what the steps themselves allocate."""
+        if getattr(self, "_gc_settled", False) and not again:
+            return
+        import gc
+        gc.collect()
+        gc.freeze()
+        self._gc_settled = True
+
+    def _batch_assembler(self):
+        if getattr(self, "_assembler", None) is None:
+            from .data.packed import DeviceBatchAssembler
+            self._assembler = DeviceBatchAssembler(self.device if self.cuda else None)
+        return self._assembler
 
     def _set_seed(self):
         seed = self.args.seed + self.get_num_updates()
@@ -303,6 +326,7 @@ class Controller:
         if self._dummy_batch is None:
             self._dummy_batch = samples[0]
         model, optimizer, reducer = self.model, self.optimizer, self.reducer
+        self._settle_gc()
         if self._graph_enabled and not dummy_batch and self._graphable(samples):
             return self._graph_train_step(samples[0])
         self._set_seed()
@@ -437,6 +461,8 @@ class Controller:
         ws = kernels.Workspace.get(self.device)
         tail = arena.tail
         tail.zero_()
+        if self._g_raw is not None:          # packed batch: the assembly kernel is the first node of the graph
+            kernels.assemble_bert_batch(self._g_raw, *self._g_raw_dims, out=self._g_sample)
         reducer.begin(sync_now=True)
         loss, sample_size, logging_output = self.task.train_step(self._g_sample, self._model, self.optimizer, False)
         tail[0:1] += loss.detach().reshape(1).float()
@@ -459,7 +485,15 @@ class Controller:
 
     def _graph_capture(self, sample):
         dev = self.device
-        self._g_sample = [t.to(dev).clone() for t in sample]
+        from .data.packed import PackedBertBatch
+        self._g_raw = None
+        if isinstance(sample, PackedBertBatch):
+            from .ops import kernels as _k
+            self._g_raw, self._g_raw_dims = sample.raw.to(dev).clone(), sample.dims
+            self._g_sample = _k.assemble_bert_batch(self._g_raw, *self._g_raw_dims)
+            sample = self._g_sample
+        else:
+            self._g_sample = [t.to(dev).clone() for t in sample]
         self._g_hyper = torch.zeros(4, dtype=torch.float32, device=dev)
         self._g_hyper_host = torch.zeros(4, dtype=torch.float32).pin_memory()
         self._g_out = torch.zeros(self._mailbox.FIELDS, dtype=torch.float64, device=dev)
@@ -479,6 +513,7 @@ class Controller:
         self._graph_launches = native.launch_count() - before      # kernels of ours inside one replay
         native.add_launch_count(-self._graph_launches)              # capture recorded them, it did not run them
         self._graph = g
+        self._settle_gc(again=True)
         print("| captured the training step in a CUDA graph ({} tensors, sample size {})".format(len(sample), ss))
 
     def _stage_hyper(self):
@@ -493,8 +528,11 @@ class Controller:
         self._set_seed()
         if self._graph is None:
             self._graph_capture(sample)
-        for dst, src in zip(self._g_sample, sample):
-            dst.copy_(src, non_blocking=True)
+        if self._g_raw is not None:
+            self._g_raw.copy_(sample[0], non_blocking=True)
+        else:
+            for dst, src in zip(self._g_sample, sample):
+                dst.copy_(src, non_blocking=True)
         self._stage_hyper()
         self._graph.replay()
         from .ops import native

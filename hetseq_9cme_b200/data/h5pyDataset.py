@@ -67,6 +67,19 @@ class BertH5pyData(torch.utils.data.Dataset):
         nsl = take("next_sentence_labels").reshape(-1)
         return [torch.from_numpy(np.ascontiguousarray(a)) for a in (input_ids, segment_ids, input_mask, labels, nsl)]
 
+    def fetch_rows_packed(self, rows: Sequence[int]) -> np.ndarray:
+        """The same rows as one packed int32 matrix for the device-side assembly (data/packed.py)."""
+        from .packed import pack_rows
+        rows = np.asarray(rows, dtype=np.int64)
+        sh = self._shard
+        take = lambda k: np.asarray(sh[k][rows] if not _is_sorted_range(rows) else sh[k][rows[0]:rows[-1] + 1])
+        return pack_rows(take("input_ids"), take("segment_ids"), take("input_mask"), take("masked_lm_positions"),
+                         take("masked_lm_ids"), take("next_sentence_labels"))
+
+    @property
+    def max_pred(self) -> int:
+        return int(self._shard["masked_lm_positions"].shape[1])
+
     def __getitem__(self, index):
         self.check_index(index)
         ids, seg, mask, lab, nsl = self.fetch_rows([index])
@@ -77,6 +90,13 @@ class BertH5pyData(torch.utils.data.Dataset):
 
     def set_epoch(self, epoch):
         pass
+
+
+def _distinct(a: np.ndarray) -> List[int]:
+    """Sorted distinct values.  Not ``np.unique``: its first call imports ``numpy.ma`` (~50 ms under the GIL), which the
+    loader thread would spend in the middle of a training step — measured as a 20-40 ms GPU bubble at the first
+    shard-spanning batch (profiles/README.md §8)."""
+    return sorted(set(a.tolist()))
 
 
 def _is_sorted_range(rows: np.ndarray) -> bool:
@@ -128,10 +148,22 @@ class ConBertH5pyData(torch.utils.data.Dataset):
         ds, local = self._locate(idx)
         if not hasattr(self.datasets[0], "fetch_rows"):
             return self.collater([self[int(i)] for i in idx])
+        if getattr(self, "packed", False) and hasattr(self.datasets[0], "fetch_rows_packed"):
+            from .packed import PackedBertBatch
+            raw = np.empty((len(idx), 0), dtype=np.int32)
+            if np.all(ds == ds[0]):
+                raw = self.datasets[int(ds[0])].fetch_rows_packed(local)
+            else:
+                first = self.datasets[int(ds[0])]
+                raw = np.empty((len(idx), 3 * first.seq_len + 2 * first.max_pred + 1), dtype=np.int32)
+                for d in _distinct(ds):
+                    raw[ds == d] = self.datasets[int(d)].fetch_rows_packed(local[ds == d])
+            first = self.datasets[int(ds[0])]
+            return PackedBertBatch.build(raw, first.seq_len, first.max_pred)
         if np.all(ds == ds[0]):
             return self.datasets[int(ds[0])].fetch_rows(local)
-        parts = [self.datasets[int(d)].fetch_rows(local[ds == d]) for d in np.unique(ds)]
-        order = np.argsort(np.concatenate([np.nonzero(ds == d)[0] for d in np.unique(ds)]))
+        parts = [self.datasets[int(d)].fetch_rows(local[ds == d]) for d in _distinct(ds)]
+        order = np.argsort(np.concatenate([np.nonzero(ds == d)[0] for d in _distinct(ds)]))
         return [torch.cat([p[k] for p in parts])[order] for k in range(len(parts[0]))]
 
     def collater(self, samples):

@@ -109,6 +109,7 @@ def _lib():
             "b200_colsum": ([I, P, LL, I, I, P, P, LL, P], I),
             "b200_softmax_fwd": ([I, P, P, P, I, I, I, I, F, P, ULL, P], I),
             "b200_softmax_bwd": ([I, P, P, I, I, I, I, F, P, ULL, P], I),
+            "b200_assemble_bert_batch": ([P, I, I, I, P, P, P, P, P, P], I),
             "b200_attn_fwd": ([POINTER(AttnArgs), P], I),
             "b200_attn_bwd": ([POINTER(AttnArgs), P], I),
             "b200_dropout": ([I, P, P, LL, F, P, ULL, P], I),
@@ -402,6 +403,20 @@ def softmax_bwd_(P, dP, B, heads, L, Lp, p_drop=0.0, seed=None, stream_id=0):
     check(_lib().b200_softmax_bwd(dtype_code(P.dtype), P.data_ptr(), dP.data_ptr(), B, heads, L, Lp, float(p_drop),
                                   _ptr(seed), stream_id, _stream()), "b200_softmax_bwd")
     return dP
+
+
+def assemble_bert_batch(raw, L, P, out=None):
+    """Packed int32 batch [B, 3L+2P+1] (device) -> [input_ids, segment_ids, input_mask, masked_lm_labels,
+    next_sentence_labels] as int64 device tensors (ref: hetseq/data/h5pyDataset.py:33-48)."""
+    assert raw.dtype == torch.int32 and raw.is_cuda and raw.is_contiguous() and raw.shape[1] == 3 * L + 2 * P + 1
+    B = raw.shape[0]
+    if out is None:
+        out = [torch.empty((B, L), dtype=torch.int64, device=raw.device) for _ in range(4)]
+        out.append(torch.empty((B,), dtype=torch.int64, device=raw.device))
+    ids, seg, mask, labels, nsl = out
+    check(_lib().b200_assemble_bert_batch(raw.data_ptr(), B, L, P, ids.data_ptr(), seg.data_ptr(), mask.data_ptr(),
+                                          labels.data_ptr(), nsl.data_ptr(), _stream()), "b200_assemble_bert_batch")
+    return out
 
 
 def _attn_args(qkv, attn_mask, B, heads, L, Lp, scale, p_drop, seed, stream_id):

@@ -196,6 +196,9 @@ _ENGINE = [
     (("--no-native",), dict(action="store_true", help="force the plain-PyTorch model path (CPU/debug only)")),
     (("--cuda-graph",), dict(action="store_true", help="capture the fixed-shape train step in a CUDA graph")),
     (("--checkpoint-activations",), dict(action="store_true", help="recompute encoder activations in backward")),
+    (("--device-batch-assembly",), dict(action="store_true",
+                                        help="ship BERT batches as one packed int32 matrix and build the int64 inputs / "
+                                             "dense MLM labels with a kernel on the GPU")),
     (("--max-predictions-per-seq",), dict(type=int, default=0, metavar="P",
                                           help="upper bound of masked positions per sequence (0: sequence length)")),
     (("--profile",), dict(action="store_true", help="emit NVTX ranges per phase")),

@@ -146,6 +146,7 @@ class LanguageModelingTask(Task):
         assert len(files) > 0, "no suitable file in split ***{}***".format(split)
         shards = [BertH5pyData(f, getattr(self.args, "max_pred_length", 512)) for f in files]
         dataset = ConBertH5pyData(shards)
+        dataset.packed = bool(getattr(self.args, "device_batch_assembly", False))
         # width of masked_lm_positions bounds the labelled positions per sequence -> capacity of the MLM head
         try:
             self._max_pred = int(shards[0]._shard["masked_lm_positions"].shape[1])

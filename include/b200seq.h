@@ -217,6 +217,16 @@ int b200_softmax_bwd(int dtype, const void* P, void* dP, int B, int heads, int L
                      const unsigned long long* seed_dev, unsigned long long stream_id, void* stream);
 
 /* ------------------------------------------------------------------------------------------------
+ * Batch assembly on the device (ref: hetseq/data/h5pyDataset.py:33-48 does this per sample on the host).
+ * raw[B][3L+2P+1] int32 = input_ids | segment_ids | input_mask | masked_lm_positions | masked_lm_ids | nsp label;
+ * outputs are the int64 [B][L] / [B] tensors of BertForPreTraining.forward, labels = -1 except at the positions
+ * before the first zero position.
+ * ---------------------------------------------------------------------------------------------- */
+int b200_assemble_bert_batch(const int* raw, int B, int L, int P, long long* input_ids, long long* segment_ids,
+                             long long* input_mask, long long* masked_lm_labels, long long* next_sentence_labels,
+                             void* stream);
+
+/* ------------------------------------------------------------------------------------------------
  * Fused multi-head attention, head size 64 (tcgen05 + TMEM + TMA; no [B,heads,L,L] tensor in HBM).
  *   forward : out[B*L, H] = dropout(softmax(Q K^T * scale + (1-mask)*-10000)) V, lse[B][heads][L] saved
  *   backward: out = dqkv[B*L, 3H] from qkv, o (forward output), dout, lse; delta[B][heads][L] is scratch

@@ -177,3 +177,32 @@ def test_file_utils_and_legacy_loader(tmp_path):
     files = sorted(os.path.join(d, f) for f in os.listdir(d) if "train" in f)
     ds = CombineBertData(files)
     assert len(ds) == 10 and len(ds[3]) == 6 and ds[3][0].shape == (16,)
+
+
+def test_packed_batches_assemble_to_the_same_tensors(tmp_path):
+    """--device-batch-assembly ships one packed int32 matrix; assembling it (host restatement of the kernel) must give
+    exactly the five tensors the per-sample path builds (ref: hetseq/data/h5pyDataset.py:33-48)."""
+    from hetseq_9cme_b200.data import synthetic
+    from hetseq_9cme_b200.data.h5pyDataset import BertH5pyData, ConBertH5pyData
+    from hetseq_9cme_b200.data.packed import PackedBertBatch, assemble_host
+    from hetseq_9cme_b200.utils import pin_sample, sample_is_empty
+    d = str(tmp_path / "pk")
+    synthetic.make_bert_shards(d, n_train_files=2, samples_per_file=24, seq_len=32, max_pred=6, vocab_size=500, test_samples=4)
+    files = sorted(os.path.join(d, f) for f in os.listdir(d) if "train" in f)
+    ds = ConBertH5pyData([BertH5pyData(f) for f in files])
+    idx = [3, 30, 7, 41, 0, 25]                                  # spans both shards, unsorted
+    plain = ds.fetch_batch(idx)
+    ds.packed = True
+    packed = ds.fetch_batch(idx)
+    assert isinstance(packed, PackedBertBatch) and packed.raw.dtype == torch.int32
+    assert packed.raw.shape == (len(idx), 3 * 32 + 2 * 6 + 1) and packed.dims == (32, 6)
+    assert not sample_is_empty(packed) and isinstance(pin_sample(packed) if torch.cuda.is_available() else packed, PackedBertBatch)
+    got = assemble_host(packed.raw, *packed.dims)
+    for a, b in zip(got, plain):
+        assert a.dtype == torch.int64 and torch.equal(a, b)
+    # semantics of the scatter: stop at the first zero position, last duplicate wins
+    raw = torch.zeros(1, 3 * 8 + 2 * 4 + 1, dtype=torch.int32)
+    raw[0, 24:28] = torch.tensor([5, 5, 0, 3])
+    raw[0, 28:32] = torch.tensor([11, 12, 13, 14])
+    labels = assemble_host(raw, 8, 4)[3][0].tolist()
+    assert labels == [-1, -1, -1, -1, -1, 12, -1, -1]

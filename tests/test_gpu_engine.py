@@ -75,3 +75,38 @@ def test_fused_step_matches_per_tensor_reference_math(tmp_path):
         assert diff < 0.2 * travelled, (k, diff)
     assert abs(c.get_meter("gnorm").avg - ref.get_meter("gnorm").avg) < 2e-2 * ref.get_meter("gnorm").avg
     assert abs(c.get_meter("train_loss").avg - ref.get_meter("train_loss").avg) < 1e-2 * abs(ref.get_meter("train_loss").avg)
+
+
+def test_device_batch_assembly_kernel_and_step(tmp_path):
+    """b200_assemble_bert_batch against its host restatement, then whole training steps fed with packed batches
+    (eager and CUDA-graph) against the ordinary five-tensor batches."""
+    from hetseq_9cme_b200.data.packed import assemble_host
+    from hetseq_9cme_b200.ops import kernels as K
+    g = torch.Generator().manual_seed(3)
+    B, L, P = 37, 128, 20
+    raw = torch.randint(0, 1000, (B, 3 * L + 2 * P + 1), generator=g, dtype=torch.int32)
+    pos = torch.randint(1, L, (B, P), generator=g, dtype=torch.int32)
+    pos[torch.rand(B, P, generator=g) < 0.15] = 0                       # early terminators
+    pos[0, :] = 0
+    pos[1, :] = 7                                                       # duplicates: the last id wins
+    raw[:, 3 * L:3 * L + P] = pos
+    want = assemble_host(raw, L, P)
+    got = K.assemble_bert_batch(raw.cuda(), L, P)
+    for a, b in zip(got, want):
+        assert a.dtype == torch.int64 and torch.equal(a.cpu(), b)
+
+    plain, it1 = _setup(tmp_path, [])
+    packed, it2 = _setup(tmp_path, ["--device-batch-assembly"])
+    graph, it3 = _setup(tmp_path, ["--device-batch-assembly", "--cuda-graph"])
+    from hetseq_9cme_b200.data.packed import PackedBertBatch
+    for _ in range(7):
+        s2 = next(it2)
+        assert isinstance(s2, PackedBertBatch)
+        plain.train_step([next(it1)]); packed.train_step([s2]); graph.train_step([next(it3)])
+    for c in (plain, packed, graph):
+        c.flush_stats()
+    assert graph._graph is not None and graph._g_raw is not None
+    a = plain.arena.master
+    for other in (packed, graph):
+        assert (a - other.arena.master).abs().max().item() <= 2e-4 * a.abs().max().item()
+    assert abs(plain.get_meter("train_loss").avg - packed.get_meter("train_loss").avg) < 1e-3

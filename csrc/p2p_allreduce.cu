@@ -74,7 +74,7 @@ __device__ __forceinline__ float block_sum(float v) {
   __syncthreads();
   float t = 0.f;
   if (threadIdx.x < 32) {
-    t = threadIdx.x < kP2PThreads / 32 ? red[threadIdx.x] : 0.f;
+    t = threadIdx.x < (blockDim.x >> 5) ? red[threadIdx.x] : 0.f;
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) t += __shfl_xor_sync(0xffffffffu, t, o);
   }
@@ -298,12 +298,22 @@ extern "C" int b200_p2p_allreduce(void* const* data_ptrs, void* const* flag_ptrs
   a.sq_out = sq_out;
   a.mc = one_shot ? nullptr : static_cast<float*>(multicast_base);
   if (blocks <= 0) blocks = 32;
+  // blocks >= 1000 encodes a narrower CTA: value = threads * 1000 + blocks (threads a multiple of 32, <= 512).
+  // Many narrow CTAs spread the copy warps over every SM instead of loading a few SMs heavily, which matters
+  // while a persistent GEMM (one CTA per SM, static tile schedule) is running next to the reduction.
+  int threads = kP2PThreads;
+  if (blocks >= 1000) {
+    threads = blocks / 1000;
+    blocks %= 1000;
+    if (threads < 32 || threads > kP2PThreads || (threads & 31) || blocks < 1) return fail(B200_ERR_ARG, "p2p_allreduce: bad threads/blocks encoding");
+  }
   if (one_shot) {
+    threads = kP2PThreads;
     const long long need = ((n >> 2) + kP2PThreads - 1) / kP2PThreads;
     if (need > 4 * num_sms()) return fail(B200_ERR_ARG, "p2p_allreduce: bucket too large for one-shot mode");
     blocks = (int)(need > 0 ? need : 1);
   }
-  p2p_allreduce_kernel<<<blocks, kP2PThreads, 0, (cudaStream_t)stream>>>(a);
+  p2p_allreduce_kernel<<<blocks, threads, 0, (cudaStream_t)stream>>>(a);
   B200_LAUNCHED("p2p_allreduce_kernel");
   return 0;
 }

@@ -76,6 +76,9 @@ class P2PReducer(BaseReducer):
         import os
         self.blocks = int(os.environ.get("B200_P2P_BLOCKS", blocks))            # while backward is still running
         self.tail_blocks = int(os.environ.get("B200_P2P_TAIL_BLOCKS", tail_blocks))  # after backward has finished
+        # CTA width of the launches that overlap backward (see b200_p2p_allreduce: threads * 1000 + blocks)
+        self.threads = int(os.environ.get("B200_P2P_THREADS", 512))
+        self.no_overlap = bool(os.environ.get("B200_P2P_NO_OVERLAP"))
         dev = arena.device
         self.flags = torch.zeros(2 * MAX_BUCKETS * MAX_RANKS, dtype=torch.int32, device=dev)
         self.counter = torch.zeros(MAX_BUCKETS, dtype=torch.int32, device=dev)
@@ -159,8 +162,16 @@ class P2PReducer(BaseReducer):
         mc = self.mc_base if (self.mc_base and n * 4 >= NVLS_MIN_BYTES) else 0
         native.check(self.lib.b200_p2p_allreduce(self.data_ptrs, self.flag_ptrs, self.counter.data_ptr(), self.rank,
                                                  self.world_size, s, n, bi, MAX_BUCKETS, self.epochs.data_ptr(), one_shot,
-                                                 self.tail_blocks if self._after_backward else self.blocks,
+                                                 self.tail_blocks if self._after_backward else self._overlap_grid(),
                                                  self.sq_ptr, mc, self._side.cuda_stream), "b200_p2p_allreduce")
+
+    def _overlap_grid(self) -> int:
+        return self.blocks if self.threads >= 512 else self.threads * 1000 + self.blocks
+
+    def ready(self, params) -> None:
+        if self.no_overlap:          # experiment switch: reduce everything after backward
+            return
+        super().ready(params)
 
     def _wait_all(self):
         torch.cuda.current_stream().wait_stream(self._side)

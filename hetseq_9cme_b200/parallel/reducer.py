@@ -37,7 +37,6 @@ class BaseReducer(GradSink):
         self._seen = set()
         self._after_backward = False
         self.fused_norm = False           # True: reductions leave sum(g^2) in arena.tail (no separate norm pass)
-        self.exposed_ms = 0.0
 
     # ---- step protocol ---------------------------------------------------------------------------
     def begin(self, sync_now: bool):

@@ -65,6 +65,21 @@ def main():
         if rank == 0:
             print("BW %s: %.3f ms for %.1f MB  -> algbw %.1f GB/s, busbw %.1f GB/s" % (
                 name, t.item(), nbytes / 1e6, nbytes / t.item() / 1e6, nbytes / t.item() / 1e6 * 2 * (world - 1) / world), flush=True)
+    # block-count sweep for the after-backward launches (whole arena, largest bucket = 94 MB word embedding)
+    for blocks in (32, 64, 128, 148, 222, 296):
+        red.tail_blocks = blocks
+        for _ in range(2):
+            red.all_reduce_flat()
+        torch.cuda.synchronize(); dist.barrier(); torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(10):
+            red.all_reduce_flat()
+        e1.record(); torch.cuda.synchronize()
+        t = torch.tensor([e0.elapsed_time(e1) / 10], device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        if rank == 0:
+            print("SWEEP tail_blocks=%3d: %.3f ms  algbw %.1f GB/s" % (blocks, t.item(), arena.numel * 4 / t.item() / 1e6), flush=True)
     if rank == 0:
         print("P2P PROBE", "PASS" if ok else "FAIL", flush=True)
     dist.barrier()

@@ -32,9 +32,11 @@ import time
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
-def _metric_name(model: str, seq_len: int) -> str:
+def _metric_name(model: str, seq_len: int, task: str = "bert") -> str:
     """BASELINE.json's headline is BERT-base phase 1 (seq 128); the other configs it lists get their own label."""
     pretty = {"bert-base": "BERT-base", "bert-large": "BERT-large"}.get(model, model)
+    if task == "ner":
+        return f"{pretty} NER fine-tuning throughput (CoNLL-2003-shaped, dynamic length)"
     phase = {128: "phase-1 ", 512: "phase-2 "}.get(seq_len, "")
     return f"{pretty} {phase}pre-training throughput (seq {seq_len})"
 
@@ -53,6 +55,9 @@ def parse(argv=None):
     ap.add_argument("--seq-len", type=int, default=128)
     ap.add_argument("--model", default="bert-base", choices=["bert-base", "bert-large", "bert-tiny"])
     ap.add_argument("--comm", default="auto")
+    ap.add_argument("--task", default="bert", choices=["bert", "ner"],
+                    help="bert: MLM+NSP pre-training (headline); ner: token-classification fine-tuning on CoNLL-shaped "
+                         "synthetic text (BASELINE.json config 5; dynamic sequence lengths, eager launches)")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-device-batch", action="store_true",
                     help="ship five int64 tensors per batch instead of one packed int32 matrix assembled on the GPU")
@@ -167,11 +172,38 @@ class ClockSampler:
                 "reasons": sorted(reasons), "samples": len(sm), "source": "nvidia-smi"}
 
 
+def _nbytes(sample) -> int:
+    """Bytes of every tensor in a (nested) batch."""
+    import torch
+    if torch.is_tensor(sample):
+        return sample.numel() * sample.element_size()
+    if isinstance(sample, dict):
+        return sum(_nbytes(v) for v in sample.values())
+    if isinstance(sample, (list, tuple)):
+        return sum(_nbytes(v) for v in sample)
+    return 0
+
+
 def _dist_env():
     rank = int(os.environ.get("RANK", "0"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     return rank, local, world
+
+
+def make_ner_args(a, data_dir, cfg_path, paths, rank, local, world):
+    from hetseq_9cme_b200 import options
+    argv = ["--task", "BertForTokenClassification", "--optimizer", "adam", "--data", data_dir, "--dict", paths["vocab"],
+            "--config_file", cfg_path, "--train_file", paths["train"], "--validation_file", paths["validation"],
+            "--test_file", paths["test"], "--max-sentences", str(a.batch), "--max-epoch", "1000", "--lr", "1e-4",
+            "--warmup-updates", "100", "--total-num-update", "100000", "--weight-decay", "0.01", "--clip-norm", "25",
+            "--fast-stat-sync", "--valid-subset", "test", "--num-workers", "2", "--save-dir", os.path.join(data_dir, "ckpt"),
+            "--no-save", "--log-format", "none", "--distributed-world-size", str(world), "--precision", a.precision,
+            "--comm", a.comm, "--disable-validation"]
+    args = options.parse_training_args(argv)
+    args.distributed_rank = rank
+    args.device_id = local
+    return args
 
 
 def make_args(a, data_dir, cfg_path, vocab_path, rank, local, world):
@@ -215,9 +247,17 @@ def run_ours(a):
                                    seq_len=a.seq_len, max_pred=max_pred, fmt="b2s", seed=1234, test_samples=a.batch)
         cfg_path = synthetic.write_bert_config(os.path.join(tmp, "bert_config.json"), **MODELS[a.model])
         vocab_path = synthetic.write_vocab(os.path.join(tmp, "vocab.txt"))
-        args = make_args(a, tmp, cfg_path, vocab_path, rank, local, world)
-        torch.manual_seed(args.seed)
-        task = tasks.LanguageModelingTask.setup_task(args)
+        if a.task == "ner":
+            paths = synthetic.make_conll(tmp, n_train=per_rank * world + a.batch, n_valid=a.batch, n_test=a.batch,
+                                         vocab_words=20000, seed=1234)
+            cfg_path = synthetic.write_bert_config(os.path.join(tmp, "bert_config.json"), vocab_size=20005, **MODELS[a.model])
+            args = make_ner_args(a, tmp, cfg_path, paths, rank, local, world)
+            torch.manual_seed(args.seed)
+            task = tasks.TASK_REGISTRY["BertForTokenClassification"].setup_task(args)
+        else:
+            args = make_args(a, tmp, cfg_path, vocab_path, rank, local, world)
+            torch.manual_seed(args.seed)
+            task = tasks.LanguageModelingTask.setup_task(args)
         task.load_dataset("test")
         model = task.build_model(args)
         controller = Controller(args, task, model)
@@ -236,7 +276,8 @@ def run_ours(a):
             from hetseq_9cme_b200.data.packed import PackedBertBatch
             if isinstance(sample, PackedBertBatch):           # raw matrix resident on the device, meta stays on the host
                 return PackedBertBatch([sample[0].cuda(non_blocking=True), sample[1]])
-            return [t.cuda(non_blocking=True) for t in sample]
+            from hetseq_9cme_b200 import utils as _u
+            return _u.move_to_cuda(sample, non_blocking=True)
 
         # ---- warm-up through the public path ------------------------------------------------------------
         staged = []
@@ -288,7 +329,7 @@ def run_ours(a):
             for s in range(a.steps):
                 sample = next(itr)
                 fetch_ms.append((time.perf_counter() - marks[-1]) * 1e3)
-                h2d += sum(t.numel() * t.element_size() for t in (sample[:1] if args.device_batch_assembly else sample))
+                h2d += _nbytes(sample[:1] if args.device_batch_assembly else sample)
                 out = controller.train_step([sample])
                 d2h += 8 * 8
                 marks.append(time.perf_counter())
@@ -324,12 +365,12 @@ def run_ours(a):
         gb = a.batch * world
         value = gb * a.steps / (dev_ms / 1e3)
         out = {
-            "metric": _metric_name(a.model, a.seq_len),
+            "metric": _metric_name(a.model, a.seq_len, a.task),
             "value": round(value, 2), "unit": "sequences/s", "n_gpus": world, "steps": a.steps, "warmup": a.warmup,
             "ms_per_step": round(dev_ms / a.steps, 4), "higher_is_better": True, "scaling": "weak",
             "vs_baseline": round(value / (PUBLISHED_SEQ_PER_SEC_PER_GPU * world), 2), "dtype": a.precision, "data": "synthetic",
             "impl": "ours",
-            "config": {"model": a.model, "global_batch": gb, "per_gpu_batch": a.batch, "seq_len": a.seq_len,
+            "config": {"model": a.model, "global_batch": gb, "per_gpu_batch": a.batch, "seq_len": (a.seq_len if a.task == "bert" else "dynamic (4-40 words per sentence, padded to the longest in the batch)"), "task": a.task,
                        "parallelism": "dp%d" % world, "optimizer": "adam (fused, fp32 master)", "dropout": 0.1,
                        "max_predictions_per_seq": max_pred, "l2_policy": "per-step working set (>= 440 MB) exceeds the 126 MB L2",
                        "timing": "CUDA events on the training stream, max over ranks", "comm": type(controller.reducer).__name__,

@@ -79,6 +79,12 @@ class P2PReducer(BaseReducer):
         # CTA width of the launches that overlap backward (see b200_p2p_allreduce: threads * 1000 + blocks)
         self.threads = int(os.environ.get("B200_P2P_THREADS", 512))
         self.no_overlap = bool(os.environ.get("B200_P2P_NO_OVERLAP"))
+        # B200_P2P_DEBUG=1: every bucket is also reduced with torch.distributed (NCCL) from a copy taken right before
+        # the launch, and compared after the step; the per-bucket epoch counters are checked against the host's count.
+        # Not usable under CUDA-graph capture (it synchronises).
+        self.debug = bool(os.environ.get("B200_P2P_DEBUG"))
+        self._debug_refs = {}
+        self.debug_checked = 0
         dev = arena.device
         self.flags = torch.zeros(2 * MAX_BUCKETS * MAX_RANKS, dtype=torch.int32, device=dev)
         self.counter = torch.zeros(MAX_BUCKETS, dtype=torch.int32, device=dev)
@@ -158,6 +164,10 @@ class P2PReducer(BaseReducer):
         ev = torch.cuda.Event()
         ev.record(torch.cuda.current_stream())
         self._side.wait_event(ev)
+        if self.debug:
+            ref = self.arena.grad[s:e].clone()
+            dist.all_reduce(ref)
+            self._debug_refs[bi] = ref
         one_shot = 1 if n * 4 <= ONE_SHOT_BYTES else 0
         mc = self.mc_base if (self.mc_base and n * 4 >= NVLS_MIN_BYTES) else 0
         native.check(self.lib.b200_p2p_allreduce(self.data_ptrs, self.flag_ptrs, self.counter.data_ptr(), self.rank,
@@ -175,6 +185,29 @@ class P2PReducer(BaseReducer):
 
     def _wait_all(self):
         torch.cuda.current_stream().wait_stream(self._side)
+        if self.debug and self._debug_refs:
+            self._debug_verify()
+
+    def _debug_verify(self):
+        """Protocol invariants after a step: every launched bucket equals the NCCL sum of the pre-launch copies, all
+        replicas hold identical bits, and each bucket's device-side epoch equals the number of steps the host issued."""
+        torch.cuda.synchronize(self.arena.device)
+        for bi, ref in sorted(self._debug_refs.items()):
+            s, e, _ = self.arena.buckets[bi]
+            got = self.arena.grad[s:e]
+            scale = float(ref.abs().max().clamp_min(1e-30))
+            err = float((got - ref).abs().max()) / scale
+            if not err < 1e-5:
+                raise RuntimeError("p2p reducer: bucket %d differs from the NCCL sum (rel err %.3e)" % (bi, err))
+            chk = torch.stack([got.double().sum(), -got.double().sum()])
+            dist.all_reduce(chk, op=dist.ReduceOp.MAX)
+            if float(chk[0]) != -float(chk[1]):
+                raise RuntimeError("p2p reducer: replicas of bucket %d are not bit-identical" % bi)
+            ep = int(self.epochs[bi])
+            if ep != self.epoch:
+                raise RuntimeError("p2p reducer: bucket %d epoch %d, host expected %d" % (bi, ep, self.epoch))
+            self.debug_checked += 1
+        self._debug_refs = {}
 
     def reduce_tail(self):
         """One-shot peer reduction of the statistics vector behind the gradients (64 floats), on the training stream."""

@@ -383,3 +383,68 @@ def test_fused_attention_matches_reference(K, dtype, L, p):
         got = dqkv.view(B * L, 3, H)[:, i]
         want = dqkv_ref.view(B * L, 3, H)[:, i]
         assert _rel(got, want) < tol * 2, name
+
+
+class _Guarded:
+    """Output tensor carved out of a larger buffer whose surroundings hold a sentinel: a cheap stand-in for
+    ``compute-sanitizer --tool memcheck`` (closed on the development pool) that catches out-of-bounds WRITES."""
+
+    PAD = 4096
+
+    def __init__(self, shape, dtype, pitch=None):
+        rows = shape[0] if len(shape) > 1 else 1
+        cols = shape[-1]
+        self.pitch = pitch or cols
+        n = rows * self.pitch
+        self.buf = torch.full((n + 2 * self.PAD,), 7.0, device="cuda").to(dtype)
+        body = self.buf[self.PAD:self.PAD + n]
+        self.view = body.view(rows, self.pitch)[:, :cols] if len(shape) > 1 else body[:cols]
+        self.rows, self.cols = rows, cols
+
+    def check(self, what):
+        b = self.buf.float()
+        assert bool((b[:self.PAD] == 7.0).all()) and bool((b[-self.PAD:] == 7.0).all()), what + ": wrote outside the buffer"
+        if self.pitch != self.cols:
+            gaps = b[self.PAD:-self.PAD].view(self.rows, self.pitch)[:, self.cols:]
+            assert bool((gaps == 7.0).all()), what + ": wrote into the pitch padding"
+        assert bool((self.view.float() != 7.0).any()), what + ": wrote nothing"
+
+
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+def test_kernels_respect_output_bounds(K, dtype):
+    from hetseq_9cme_b200.ops.gemm import gemm
+    torch.manual_seed(3)
+    ws = K.Workspace.get("cuda")
+    ws.set_seed(11)
+    # GEMM with ragged M / N (TMA store clipping) into a pitched output
+    for (M, N, Kd) in [(100, 72, 64), (257, 200, 96), (4096, 24, 128)]:
+        a = torch.randn(M, Kd, device="cuda").to(dtype)
+        b = torch.randn(N, Kd, device="cuda").to(dtype)
+        g = _Guarded((M, N), dtype, pitch=(N + 7) // 8 * 8 + 8)
+        gemm(a, b, out=g.view)
+        torch.cuda.synchronize()
+        g.check("gemm %dx%dx%d" % (M, N, Kd))
+        assert _rel(g.view, a.float() @ b.float().t()) < (2e-3 if dtype == torch.float32 else 2e-2)
+    # fused attention, ragged L (TMA store clipping of rows >= L, head-strided writes into [B*L, 3H])
+    for L in (72, 128, 200):
+        B, h = 2, 3
+        H = h * 64
+        qkv = torch.randn(B * L, 3 * H, device="cuda").to(dtype)
+        dout = torch.randn(B * L, H, device="cuda").to(dtype)
+        go = _Guarded((B * L, H), dtype)
+        o, lse = K.attn_fwd(qkv, None, B, h, L, 0.125, 0.1, ws.seed, 3, out=go.view)
+        gd = _Guarded((B * L, 3 * H), dtype)
+        K.attn_bwd(qkv, o, dout, lse, None, B, h, L, 0.125, 0.1, ws.seed, 3, out=gd.view)
+        torch.cuda.synchronize()
+        go.check("attn_fwd L=%d" % L)
+        gd.check("attn_bwd L=%d" % L)
+        assert bool(torch.isfinite(gd.view.float()).all()) and bool((gd.view.float() != 7.0).all())
+    # batch assembly
+    if dtype == torch.float32:
+        B, L, P = 5, 96, 12
+        raw = torch.randint(1, 90, (B, 3 * L + 2 * P + 1), dtype=torch.int32, device="cuda")
+        outs = [torch.full((B * L + 64,), 7, dtype=torch.int64, device="cuda") for _ in range(4)]
+        nsl = torch.full((B + 64,), 7, dtype=torch.int64, device="cuda")
+        K.assemble_bert_batch(raw, L, P, out=[t[:B * L].view(B, L) for t in outs] + [nsl[:B]])
+        torch.cuda.synchronize()
+        assert all(bool((t[B * L:] == 7).all()) for t in outs) and bool((nsl[B:] == 7).all())

@@ -23,6 +23,7 @@
 #include <unordered_map>
 #include <string>
 #include <cstring>
+#include <cstdlib>
 
 namespace b200 {
 
@@ -67,7 +68,10 @@ __device__ __forceinline__ float to_f<float>(float v) { return v; }
 template <>
 __device__ __forceinline__ float to_f<__nv_bfloat16>(__nv_bfloat16 v) { return __bfloat162float(v); }
 
-template <typename TIn, typename TOut, int BN, bool A_MN, bool B_MN, int STAGES, bool EPI_SOFTMAX>
+// CTA2: the kernel is launched in clusters of two CTAs that share every tcgen05.mma (cta_group::2, M = 256):
+// CTA r of the pair owns rows m0 + 128 r of the 256 x BN tile and loads only rows r*BN/2 .. of the B tile; the leader
+// (r = 0) owns the smem-full / TMEM-empty barriers and issues the MMAs, commits are multicast to both CTAs.
+template <typename TIn, typename TOut, int BN, bool A_MN, bool B_MN, int STAGES, bool EPI_SOFTMAX, bool CTA2 = false>
 __global__ void __launch_bounds__(kGemmThreads, 1)
 gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                     const __grid_constant__ CUtensorMap tmD, const __grid_constant__ CUtensorMap tmD2,
@@ -77,13 +81,15 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
   constexpr int UK = 32 / ES;         // K per tcgen05.mma (8 tf32 / 16 bf16)
   constexpr int EA = 128 / ES;        // elements per 128 B along MN (MN-major slab width)
   constexpr int A_BYTES = kBM * 128;
-  constexpr int B_BYTES = BN * 128;
+  constexpr int B_ROWS = CTA2 ? BN / 2 : BN;   // rows of the B tile held by this CTA
+  constexpr int B_BYTES = B_ROWS * 128;
+  static_assert(!(CTA2 && EPI_SOFTMAX), "softmax epilogues run single-CTA");
   constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
   constexpr int SLAB_BYTES = BK * 128;
   constexpr uint32_t ACC_STRIDE = (BN <= 64) ? 64 : (BN <= 128 ? 128 : 256);
   constexpr uint32_t TMEM_COLS = 2 * ACC_STRIDE;
   constexpr MmaKind KIND = (ES == 4) ? MmaKind::TF32 : MmaKind::F16;
-  constexpr uint32_t IDESC = make_idesc(ES == 4 ? 2u : 1u, A_MN, B_MN, kBM, BN);
+  constexpr uint32_t IDESC = make_idesc(ES == 4 ? 2u : 1u, A_MN, B_MN, CTA2 ? 2 * kBM : kBM, BN);
   constexpr int OS = sizeof(TOut);
   constexpr int CW = 128 / OS;        // output columns per 128 B staging row (32 fp32 / 64 bf16)
   static_assert(BN % CW == 0, "BN must be a multiple of the staging chunk width");
@@ -102,6 +108,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
+  const uint32_t crank = CTA2 ? cluster_ctarank() : 0u;      // 0 = leader of the pair
 
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&tmA);
@@ -113,29 +120,38 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
     }
     for (int a = 0; a < 2; ++a) {
       mbar_init(&tmem_full[a], 1);
-      mbar_init(&tmem_empty[a], 4);
+      mbar_init(&tmem_empty[a], CTA2 ? 8 : 4);          // epilogue warps of both CTAs release the leader's slot
     }
     for (int a = 0; a < 8; ++a) mbar_init(&aux_bar[a], 1);
     fence_barrier_init();
   }
-  if (warp == 1) tmem_alloc<TMEM_COLS>(tmem_slot);
+  if constexpr (CTA2) {
+    cluster_sync_all();                  // both CTAs' barriers are initialised before anything can signal them
+    if (warp == 1) tmem_alloc_2sm<TMEM_COLS>(tmem_slot);
+  } else {
+    if (warp == 1) tmem_alloc<TMEM_COLS>(tmem_slot);
+  }
   tcgen05_fence_before();
   __syncthreads();
   tcgen05_fence_after();
   const uint32_t tmem_base = *tmem_slot;
 
+  // CTA2: args.num_m counts 256-row pair tiles and the pair index replaces blockIdx.x in the tile schedule
   const int num_tiles = args.nbatch * args.num_m * args.num_n * args.splits;
+  const int sched_id = CTA2 ? (int)(blockIdx.x >> 1) : (int)blockIdx.x;
+  const int sched_n = CTA2 ? (int)(gridDim.x >> 1) : (int)gridDim.x;
+  constexpr int TILE_M = CTA2 ? 2 * kBM : kBM;
 
   if (warp == 0) {
     // ===================================== TMA producer =====================================
     if (lane == 0) {
       uint32_t it = 0;
-      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+      for (int tile = sched_id; tile < num_tiles; tile += sched_n) {
         const int split = tile % args.splits;
         int rest = tile / args.splits;
-        const int n0 = (rest % args.num_n) * BN;
+        const int n0 = (rest % args.num_n) * BN + (int)crank * B_ROWS;          // this CTA's share of the B tile
         rest /= args.num_n;
-        const int m0 = (rest % args.num_m) * kBM;
+        const int m0 = (rest % args.num_m) * TILE_M + (int)crank * kBM;       // this CTA's 128 rows
         const int bt = rest / args.num_m;
         const int b0 = bt % args.nb0, b1 = bt / args.nb0;
         const int kb0 = split * args.kb_per_split;
@@ -144,31 +160,49 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
           const uint32_t s = it % STAGES;
           const uint32_t ph = (it / STAGES) & 1;
           mbar_wait(&empty_bar[s], ph ^ 1);
-          mbar_arrive_expect_tx(&full_bar[s], STAGE_BYTES);
           uint8_t* sA = smem_stage + s * STAGE_BYTES;
           uint8_t* sB = sA + A_BYTES;
           const int k0 = kb * BK;
-          if constexpr (!A_MN) {
-            tma_load_4d(sA, &tmA, &full_bar[s], k0, m0, b0, b1);
-          } else {
+          if constexpr (CTA2) {
+            // the leader's barrier collects the bytes of both CTAs; only the leader arms it
+            if (crank == 0) mbar_arrive_expect_tx(&full_bar[s], 2 * STAGE_BYTES);
+            const uint32_t fb = mapa_u32(smem_u32(&full_bar[s]), 0);
+            if constexpr (!A_MN) {
+              tma_load_4d_2sm(sA, &tmA, fb, k0, m0, b0, b1);
+            } else {
 #pragma unroll
-            for (int sl = 0; sl < kBM / EA; ++sl) tma_load_4d(sA + sl * SLAB_BYTES, &tmA, &full_bar[s], m0 + sl * EA, k0, b0, b1);
-          }
-          if constexpr (!B_MN) {
-            tma_load_4d(sB, &tmB, &full_bar[s], k0, n0, b0, b1);
-          } else {
+              for (int sl = 0; sl < kBM / EA; ++sl) tma_load_4d_2sm(sA + sl * SLAB_BYTES, &tmA, fb, m0 + sl * EA, k0, b0, b1);
+            }
+            if constexpr (!B_MN) {
+              tma_load_4d_2sm(sB, &tmB, fb, k0, n0, b0, b1);
+            } else {
 #pragma unroll
-            for (int sl = 0; sl < BN / EA; ++sl) tma_load_4d(sB + sl * SLAB_BYTES, &tmB, &full_bar[s], n0 + sl * EA, k0, b0, b1);
+              for (int sl = 0; sl < B_ROWS / EA; ++sl) tma_load_4d_2sm(sB + sl * SLAB_BYTES, &tmB, fb, n0 + sl * EA, k0, b0, b1);
+            }
+          } else {
+            mbar_arrive_expect_tx(&full_bar[s], STAGE_BYTES);
+            if constexpr (!A_MN) {
+              tma_load_4d(sA, &tmA, &full_bar[s], k0, m0, b0, b1);
+            } else {
+#pragma unroll
+              for (int sl = 0; sl < kBM / EA; ++sl) tma_load_4d(sA + sl * SLAB_BYTES, &tmA, &full_bar[s], m0 + sl * EA, k0, b0, b1);
+            }
+            if constexpr (!B_MN) {
+              tma_load_4d(sB, &tmB, &full_bar[s], k0, n0, b0, b1);
+            } else {
+#pragma unroll
+              for (int sl = 0; sl < BN / EA; ++sl) tma_load_4d(sB + sl * SLAB_BYTES, &tmB, &full_bar[s], n0 + sl * EA, k0, b0, b1);
+            }
           }
         }
       }
     }
   } else if (warp == 1) {
     // ===================================== MMA issuer =======================================
-    if (lane == 0) {
+    if (lane == 0 && crank == 0) {
       uint32_t it = 0;
       uint32_t tcount = 0;
-      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++tcount) {
+      for (int tile = sched_id; tile < num_tiles; tile += sched_n, ++tcount) {
         const int split = tile % args.splits;
         const int kb0 = split * args.kb_per_split;
         const int kb1 = min(args.kb_total, kb0 + args.kb_per_split);
@@ -195,11 +229,16 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
             // advance inside the stage: K-major -> 32 B along the swizzled row; MN-major -> UK rows of 128 B
             const uint64_t a_off = A_MN ? (uint64_t)((j * UK * 128) >> 4) : (uint64_t)((j * 32) >> 4);
             const uint64_t b_off = B_MN ? (uint64_t)((j * UK * 128) >> 4) : (uint64_t)((j * 32) >> 4);
-            tcgen05_mma_ss<KIND>(d_tmem, a_desc + a_off, b_desc + b_off, IDESC, (kb > kb0 || j > 0) ? 1u : 0u);
+            if constexpr (CTA2) tcgen05_mma_ss_2sm<KIND>(d_tmem, a_desc + a_off, b_desc + b_off, IDESC, (kb > kb0 || j > 0) ? 1u : 0u);
+            else tcgen05_mma_ss<KIND>(d_tmem, a_desc + a_off, b_desc + b_off, IDESC, (kb > kb0 || j > 0) ? 1u : 0u);
           }
-          tcgen05_commit(&empty_bar[s]);   // frees the smem stage once these MMAs have read it
+          // frees the smem stage (in both CTAs of a pair) once these MMAs have read it
+          if constexpr (CTA2) tcgen05_commit_2sm(&empty_bar[s], 3);
+          else tcgen05_commit(&empty_bar[s]);
         }
-        tcgen05_commit(&tmem_full[acc]);   // accumulator complete -> epilogue
+        // accumulator complete -> epilogue (of both CTAs)
+        if constexpr (CTA2) tcgen05_commit_2sm(&tmem_full[acc], 3);
+        else tcgen05_commit(&tmem_full[acc]);
       }
     }
   } else {
@@ -225,12 +264,12 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
     };
     uint32_t ax = 0;                       // aux-tile sequence counter of the softmax-backward epilogue
 
-    for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++tcount) {
+    for (int tile = sched_id; tile < num_tiles; tile += sched_n, ++tcount) {
       const int split = tile % args.splits;
       int rest = tile / args.splits;
       const int n0 = (rest % args.num_n) * BN;
       rest /= args.num_n;
-      const int m0 = (rest % args.num_m) * kBM;
+      const int m0 = (rest % args.num_m) * TILE_M + (int)crank * kBM;
       const int bt = rest / args.num_m;
       const int b0 = bt % args.nb0, b1 = bt / args.nb0;
       const uint32_t acc = tcount & 1;
@@ -504,17 +543,32 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
       // all TMEM reads of this accumulator slot are done -> hand it back to the MMA warp
       tcgen05_fence_before();
       __syncwarp();
-      if (lane == 0) mbar_arrive(&tmem_empty[acc]);
+      if (lane == 0) {
+        if constexpr (CTA2) {
+          if (crank == 0) mbar_arrive(&tmem_empty[acc]);
+          else mbar_arrive_cluster(mapa_u32(smem_u32(&tmem_empty[acc]), 0));
+        } else {
+          mbar_arrive(&tmem_empty[acc]);
+        }
+      }
     }
     if (lane == 0) tma_store_wait_read<0>();
     __syncwarp();
   }
 
   tcgen05_fence_before();
-  __syncthreads();
-  if (warp == 1) {
-    tcgen05_fence_after();
-    tmem_dealloc<TMEM_COLS>(tmem_base);
+  if constexpr (CTA2) {
+    cluster_sync_all();       // neither CTA may free TMEM (or exit, its smem is read by the peer's MMAs) before both are done
+    if (warp == 1) {
+      tcgen05_fence_after();
+      tmem_dealloc_2sm<TMEM_COLS>(tmem_base);
+    }
+  } else {
+    __syncthreads();
+    if (warp == 1) {
+      tcgen05_fence_after();
+      tmem_dealloc<TMEM_COLS>(tmem_base);
+    }
   }
 }
 
@@ -568,13 +622,45 @@ int make_tmap_4d(CUtensorMap* out, const void* ptr, int elem_bytes, bool is_bf16
 // ------------------------------------------------------------------------------------------------
 // host side: dispatch
 // ------------------------------------------------------------------------------------------------
-template <int BN>
+template <int BN, bool CTA2 = false>
 constexpr int stages_for() {
   // 227 KB usable; keep 32 KB for the epilogue staging ring, ~2 KB for alignment slack + barriers.
-  constexpr int stage = kBM * 128 + BN * 128;
+  constexpr int stage = kBM * 128 + (CTA2 ? BN / 2 : BN) * 128;
   constexpr int avail = 232448 - kEpiBytes - 2048;
   constexpr int s = avail / stage;
   return s > 8 ? 8 : s;
+}
+
+// CTA-pair variant: clusters of two CTAs, one pair per TPC, 256 x BN tiles (see the kernel's CTA2 comment)
+template <typename TIn, typename TOut, int BN, bool A_MN, bool B_MN>
+static int launch_gemm_cta2(const CUtensorMap& tA, const CUtensorMap& tB, const CUtensorMap& tD, const CUtensorMap& tD2,
+                            const CUtensorMap& tX, const GemmArgs& args, cudaStream_t stream) {
+  constexpr int STAGES = stages_for<BN, true>();
+  constexpr int smem = STAGES * (kBM * 128 + (BN / 2) * 128) + kEpiBytes + 1024 /*align*/ + (2 * STAGES + 12) * 8 + 16;
+  auto kern = gemm_tcgen05_kernel<TIn, TOut, BN, A_MN, B_MN, STAGES, false, true>;
+  static bool attr_set = false;
+  if (!attr_set) {
+    B200_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    attr_set = true;
+  }
+  const long long tiles = (long long)args.nbatch * args.num_m * args.num_n * args.splits;     // pair tiles
+  const int pairs = num_sms() / 2;
+  const int grid = 2 * (int)(tiles < pairs ? tiles : pairs);
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3(grid);
+  cfg.blockDim = dim3(kGemmThreads);
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = stream;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = 2;
+  attr[0].val.clusterDim.y = 1;
+  attr[0].val.clusterDim.z = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  B200_CUDA(cudaLaunchKernelEx(&cfg, kern, tA, tB, tD, tD2, tX, args));
+  B200_LAUNCHED("gemm_tcgen05_kernel<cta2>");
+  return 0;
 }
 
 template <typename TIn, typename TOut, int BN, bool A_MN, bool B_MN>
@@ -612,6 +698,15 @@ static int launch_gemm(const CUtensorMap& tA, const CUtensorMap& tB, const CUten
 }
 
 template <typename TIn, typename TOut, int BN>
+static int dispatch_major_cta2(bool a_mn, bool b_mn, const CUtensorMap& tA, const CUtensorMap& tB, const CUtensorMap& tD,
+                               const CUtensorMap& tD2, const CUtensorMap& tX, const GemmArgs& args, cudaStream_t stream) {
+  if (!a_mn && !b_mn) return launch_gemm_cta2<TIn, TOut, BN, false, false>(tA, tB, tD, tD2, tX, args, stream);
+  if (!a_mn && b_mn) return launch_gemm_cta2<TIn, TOut, BN, false, true>(tA, tB, tD, tD2, tX, args, stream);
+  if (a_mn && b_mn) return launch_gemm_cta2<TIn, TOut, BN, true, true>(tA, tB, tD, tD2, tX, args, stream);
+  return launch_gemm_cta2<TIn, TOut, BN, true, false>(tA, tB, tD, tD2, tX, args, stream);
+}
+
+template <typename TIn, typename TOut, int BN>
 static int dispatch_major(bool a_mn, bool b_mn, const CUtensorMap& tA, const CUtensorMap& tB, const CUtensorMap& tD,
                           const CUtensorMap& tD2, const CUtensorMap& tX, const GemmArgs& args, cudaStream_t stream) {
   if (!a_mn && !b_mn) return launch_gemm<TIn, TOut, BN, false, false>(tA, tB, tD, tD2, tX, args, stream);
@@ -621,8 +716,15 @@ static int dispatch_major(bool a_mn, bool b_mn, const CUtensorMap& tA, const CUt
 }
 
 template <typename TIn, typename TOut>
-static int dispatch_bn(int bn, bool a_mn, bool b_mn, const CUtensorMap& tA, const CUtensorMap& tB, const CUtensorMap& tD,
+static int dispatch_bn(int bn, bool cta2, bool a_mn, bool b_mn, const CUtensorMap& tA, const CUtensorMap& tB, const CUtensorMap& tD,
                        const CUtensorMap& tD2, const CUtensorMap& tX, const GemmArgs& args, cudaStream_t stream) {
+  if (cta2) {
+    switch (bn) {
+      case 128: return dispatch_major_cta2<TIn, TOut, 128>(a_mn, b_mn, tA, tB, tD, tD2, tX, args, stream);
+      case 256: return dispatch_major_cta2<TIn, TOut, 256>(a_mn, b_mn, tA, tB, tD, tD2, tX, args, stream);
+    }
+    return fail(B200_ERR_ARG, "cta-pair GEMM supports BN 128 / 256, not %d", bn);
+  }
   switch (bn) {
     case 64: return dispatch_major<TIn, TOut, 64>(a_mn, b_mn, tA, tB, tD, tD2, tX, args, stream);
     case 128: return dispatch_major<TIn, TOut, 128>(a_mn, b_mn, tA, tB, tD, tD2, tX, args, stream);
@@ -653,6 +755,18 @@ static int choose_bn(int M, int N, int splits, int nbatch) {
     }
   }
   return best_bn;
+}
+
+constexpr bool kCta2Default = false;   // flipped once the full GPU suite and the step benchmark have run with it
+
+// Does the CTA-pair kernel pay for this problem?  It halves the B traffic per SM but schedules 256-row tiles on
+// 74 pairs; with few tiles the coarser granularity costs more than the bandwidth saves.
+static bool cta2_pays(int M, int N, int bn, int splits, int nbatch) {
+  const int sms = num_sms();
+  const long long t1 = (long long)((M + 127) / 128) * ((N + bn - 1) / bn) * splits * nbatch;
+  const long long t2 = (long long)((M + 255) / 256) * ((N + bn - 1) / bn) * splits * nbatch;
+  const long long w1 = (t1 + sms - 1) / sms, w2 = (t2 + sms / 2 - 1) / (sms / 2);
+  return w2 <= w1;          // same number of waves (or fewer) -> the pair kernel is never slower on paper
 }
 
 static int gemm_impl(const b200_gemm_desc* d, cudaStream_t stream) {
@@ -743,13 +857,23 @@ static int gemm_impl(const b200_gemm_desc* d, cudaStream_t stream) {
                          : (d->bn > 0 ? d->bn : (joint_bn > 0 ? joint_bn : choose_bn(d->M, d->N, splits, nbatch)));
   if (epi_mode != 0) bn = d->N <= 64 ? 64 : (d->N <= 128 ? 128 : (d->N <= 192 ? 192 : 256));
   if (bn != 64 && bn != 128 && bn != 192 && bn != 256) return fail(B200_ERR_ARG, "gemm: bn must be 64/128/192/256");
+  // CTA pairs (cta_group::2): a CTA ingests A + B/2 per k-block instead of A + B.  B200_GEMM_CTA2 = 0 / 1 forces it.
+  bool cta2 = false;
+  {
+    const char* e = getenv("B200_GEMM_CTA2");      // read per call so that tests can flip it
+    const int env = e ? atoi(e) : -1;
+    const bool can = epi_mode == 0 && (bn == 128 || bn == 256) && d->M > kBM;
+    cta2 = can && (env == 1 || (env < 0 && kCta2Default && cta2_pays(d->M, d->N, bn, splits, nbatch)));
+  }
+  const int tile_m = cta2 ? 2 * kBM : kBM;
+  const int num_m_eff = (d->M + tile_m - 1) / tile_m;
 
   CUtensorMap tA, tB, tD, tD2;
   int rc;
   if (!d->a_mn) rc = make_tmap_4d(&tA, d->A, es, in_bf16, d->M, d->K, d->lda, BK, kBM, false, nb0, d->sa0, nb1, d->sa1);
   else rc = make_tmap_4d(&tA, d->A, es, in_bf16, d->K, d->M, d->lda, EA, BK, es == 4, nb0, d->sa0, nb1, d->sa1);
   if (rc) return rc;
-  if (!d->b_mn) rc = make_tmap_4d(&tB, d->B, es, in_bf16, d->N, d->K, d->ldb, BK, bn, false, nb0, d->sb0, nb1, d->sb1);
+  if (!d->b_mn) rc = make_tmap_4d(&tB, d->B, es, in_bf16, d->N, d->K, d->ldb, BK, cta2 ? bn / 2 : bn, false, nb0, d->sb0, nb1, d->sb1);
   else rc = make_tmap_4d(&tB, d->B, es, in_bf16, d->K, d->N, d->ldb, EA, BK, es == 4, nb0, d->sb0, nb1, d->sb1);
   if (rc) return rc;
   const int CW = 128 / os;
@@ -769,7 +893,7 @@ static int gemm_impl(const b200_gemm_desc* d, cudaStream_t stream) {
 
   GemmArgs a;
   a.M = d->M; a.N = d->N; a.K = d->K;
-  a.num_m = num_m;
+  a.num_m = num_m_eff;
   a.num_n = (d->N + bn - 1) / bn;
   a.splits = splits;
   a.nb0 = nb0;
@@ -793,9 +917,9 @@ static int gemm_impl(const b200_gemm_desc* d, cudaStream_t stream) {
   if (epi_mode != 0) a.aux_mode = B200_AUX_NONE;     // aux is consumed by the softmax-backward epilogue itself
 
   switch (d->dtype) {
-    case B200_F32_TF32: return dispatch_bn<float, float>(bn, d->a_mn, d->b_mn, tA, tB, tD, tD2, tX, a, stream);
-    case B200_BF16: return dispatch_bn<__nv_bfloat16, __nv_bfloat16>(bn, d->a_mn, d->b_mn, tA, tB, tD, tD2, tX, a, stream);
-    case B200_BF16_F32OUT: return dispatch_bn<__nv_bfloat16, float>(bn, d->a_mn, d->b_mn, tA, tB, tD, tD2, tX, a, stream);
+    case B200_F32_TF32: return dispatch_bn<float, float>(bn, cta2, d->a_mn, d->b_mn, tA, tB, tD, tD2, tX, a, stream);
+    case B200_BF16: return dispatch_bn<__nv_bfloat16, __nv_bfloat16>(bn, cta2, d->a_mn, d->b_mn, tA, tB, tD, tD2, tX, a, stream);
+    case B200_BF16_F32OUT: return dispatch_bn<__nv_bfloat16, float>(bn, cta2, d->a_mn, d->b_mn, tA, tB, tD, tD2, tX, a, stream);
   }
   return fail(B200_ERR_ARG, "gemm: unknown dtype %d", d->dtype);
 }

@@ -448,3 +448,37 @@ def test_kernels_respect_output_bounds(K, dtype):
         K.assemble_bert_batch(raw, L, P, out=[t[:B * L].view(B, L) for t in outs] + [nsl[:B]])
         torch.cuda.synchronize()
         assert all(bool((t[B * L:] == 7).all()) for t in outs) and bool((nsl[B:] == 7).all())
+
+
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+@pytest.mark.parametrize("majors", [(False, False), (False, True), (True, True), (True, False)])
+def test_gemm_cta_pair_matches_single_cta(dtype, majors, monkeypatch):
+    """The cta_group::2 kernel (two CTAs share each tcgen05.mma, each loads half of B) against the single-CTA kernel and
+    fp64, on shapes with ragged M / N, a bias + GELU epilogue and fp32 accumulation into an existing output."""
+    from hetseq_9cme_b200.ops import native as N
+    from hetseq_9cme_b200.ops.gemm import gemm
+    a_mn, b_mn = majors
+    torch.manual_seed(4)
+    for (M, Nn, Kd, bn) in [(512, 256, 128, 256), (1000, 200, 96, 128), (4096, 768, 768, 0), (300, 520, 64, 256)]:
+        a = torch.randn((Kd, M) if a_mn else (M, Kd), device="cuda").to(dtype)
+        b = torch.randn((Kd, Nn) if b_mn else (Nn, Kd), device="cuda").to(dtype)
+        bias = torch.randn(Nn, device="cuda").to(dtype)
+        outs = {}
+        for flag in ("0", "1"):
+            monkeypatch.setenv("B200_GEMM_CTA2", flag)
+            outs[flag] = gemm(a, b, a_mn=a_mn, b_mn=b_mn, bias=bias, act=N.ACT_GELU, bn=bn)
+        torch.cuda.synchronize()
+        A = (a.t() if a_mn else a).double()
+        B = (b.t() if b_mn else b).double()
+        ref = torch.nn.functional.gelu(A @ B.t() + bias.double())
+        tol = 2e-3 if dtype == torch.float32 else 2e-2
+        assert _rel(outs["1"], ref) < tol, (M, Nn, Kd)
+        assert _rel(outs["1"], outs["0"].double()) < tol / 4
+    # accumulate (weight-gradient) mode with split-K
+    monkeypatch.setenv("B200_GEMM_CTA2", "1")
+    x = torch.randn(4096, 768, device="cuda").to(dtype)
+    dy = torch.randn(4096, 512, device="cuda").to(dtype)
+    acc = torch.ones(512, 768, device="cuda")
+    gemm(dy, x, a_mn=True, b_mn=True, out=acc, out_dtype=torch.float32, accumulate=True)
+    torch.cuda.synchronize()
+    assert _rel(acc, 1.0 + dy.double().t() @ x.double()) < (2e-3 if dtype == torch.float32 else 1e-2)

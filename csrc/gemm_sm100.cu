@@ -757,16 +757,17 @@ static int choose_bn(int M, int N, int splits, int nbatch) {
   return best_bn;
 }
 
-constexpr bool kCta2Default = false;   // flipped once the full GPU suite and the step benchmark have run with it
-
-// Does the CTA-pair kernel pay for this problem?  It halves the B traffic per SM but schedules 256-row tiles on
-// 74 pairs; with few tiles the coarser granularity costs more than the bandwidth saves.
-static bool cta2_pays(int M, int N, int bn, int splits, int nbatch) {
+// Does the CTA-pair kernel pay for this problem?  It halves the B traffic per SM but schedules 256-row tiles on 74
+// pairs.  Measured on B200 (profiles/README.md §9): 8-18 % faster on 8192^3 (except fp32 with MN-major A: 17 % slower),
+// 4-7 % on [4096 x 3072 x 768], nothing on the narrower BERT-base GEMMs, and a BERT-base training step with it forced
+// everywhere is 1.3 % SLOWER (coarser tiles with < 3 waves), a BERT-large step 0.5 % faster.  Hence: large problems only.
+static bool cta2_pays(int M, int N, int bn, int splits, int nbatch, bool fp32_a_mn) {
+  if (fp32_a_mn) return false;
   const int sms = num_sms();
   const long long t1 = (long long)((M + 127) / 128) * ((N + bn - 1) / bn) * splits * nbatch;
   const long long t2 = (long long)((M + 255) / 256) * ((N + bn - 1) / bn) * splits * nbatch;
   const long long w1 = (t1 + sms - 1) / sms, w2 = (t2 + sms / 2 - 1) / (sms / 2);
-  return w2 <= w1;          // same number of waves (or fewer) -> the pair kernel is never slower on paper
+  return w2 <= w1 && w2 >= 4;
 }
 
 static int gemm_impl(const b200_gemm_desc* d, cudaStream_t stream) {
@@ -863,7 +864,7 @@ static int gemm_impl(const b200_gemm_desc* d, cudaStream_t stream) {
     const char* e = getenv("B200_GEMM_CTA2");      // read per call so that tests can flip it
     const int env = e ? atoi(e) : -1;
     const bool can = epi_mode == 0 && (bn == 128 || bn == 256) && d->M > kBM;
-    cta2 = can && (env == 1 || (env < 0 && kCta2Default && cta2_pays(d->M, d->N, bn, splits, nbatch)));
+    cta2 = can && (env == 1 || (env < 0 && cta2_pays(d->M, d->N, bn, splits, nbatch, !in_bf16 && d->a_mn)));
   }
   const int tile_m = cta2 ? 2 * kBM : kBM;
   const int num_m_eff = (d->M + tile_m - 1) / tile_m;

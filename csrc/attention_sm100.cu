@@ -529,7 +529,7 @@ static int attn_fwd_impl(const b200_attn_args* g, cudaStream_t st) {
   a.scale = g->scale; a.p_drop = g->p_drop; a.mask = g->attn_mask; a.seed_dev = g->seed_dev; a.stream_id = g->stream_id;
   a.out = g->out; a.ld_out = g->ld_out; a.lse = g->lse;
   dim3 grid((g->L + 127) / 128, g->heads, g->B);
-  attn_fwd_wide_kernel<T><<<grid, kWideThreads, fwd_smem<T>(), st>>>(tq, tv, to, a);
+  B200_CUDA(launch_pdl(attn_fwd_wide_kernel<T>, grid, dim3(kWideThreads), fwd_smem<T>(), st, 1, tq, tv, to, a));
   B200_LAUNCHED("attn_fwd_wide_kernel");
   return 0;
 }
@@ -554,7 +554,8 @@ static int attn_bwd_impl(const b200_attn_args* g, cudaStream_t st) {
   a.o = g->o; a.dout = g->dout; a.ld_o = g->ld_o;
   if (g->L <= 128) {       // one kernel computes all three gradients of a (batch, head)
     if (int e = head_map<T>(&tout, g->out, g->B, 3 * g->heads, g->L, g->ld_out, false)) return e;
-    attn_bwd_block_kernel<T><<<dim3(g->heads, g->B), kWideThreads, blk_smem<T>(), st>>>(tq, tmn, tdo, tdomn, tout, a);
+    B200_CUDA(launch_pdl(attn_bwd_block_kernel<T>, dim3(g->heads, g->B), dim3(kWideThreads), blk_smem<T>(), st, 1, tq, tmn, tdo,
+                         tdomn, tout, a));
     B200_LAUNCHED("attn_bwd_block_kernel");
     return 0;
   }

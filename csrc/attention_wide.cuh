@@ -154,6 +154,7 @@ attn_fwd_wide_kernel(const __grid_constant__ CUtensorMap tmQK, const __grid_cons
   const int q0 = blockIdx.x * 128;
   const int qrow = q0 + row;
   const bool qlive = qrow < a.L;
+  pdl_trigger();
 
   if (t == 0) {
     tma_prefetch_desc(&tmQK);
@@ -161,6 +162,7 @@ attn_fwd_wide_kernel(const __grid_constant__ CUtensorMap tmQK, const __grid_cons
     tma_prefetch_desc(&tmOut);
     mbar_init(bar_q, 1); mbar_init(bar_k, 1); mbar_init(bar_v, 1); mbar_init(bar_s, 1); mbar_init(bar_pv, 1);
     fence_barrier_init();
+    pdl_wait();                                   // qkv comes from the previous kernel
     mbar_arrive_expect_tx(bar_q, OPB);
     load_tile<T>(sQ, &tmQK, bar_q, q0, h, b);
   }
@@ -168,6 +170,7 @@ attn_fwd_wide_kernel(const __grid_constant__ CUtensorMap tmQK, const __grid_cons
   tcgen05_fence_before();
   __syncthreads();
   tcgen05_fence_after();
+  pdl_wait();
   const uint32_t tmem = *tmem_slot;
   const uint32_t tS = tmem + ((uint32_t)(lq * 32) << 16) + cq * 32;
   const uint32_t tO = tmem + ((uint32_t)(lq * 32) << 16) + 128 + cq * 16;
@@ -338,6 +341,7 @@ attn_bwd_block_kernel(const __grid_constant__ CUtensorMap tmQK, const __grid_con
   const int row = lq * 32 + lane;
   const int h = blockIdx.x, b = blockIdx.y;
   const long long bh = (long long)b * a.heads + h;
+  pdl_trigger();
 
   if (t == 0) {
     tma_prefetch_desc(&tmQK); tma_prefetch_desc(&tmMN); tma_prefetch_desc(&tmdO); tma_prefetch_desc(&tmdOmn);
@@ -345,6 +349,7 @@ attn_bwd_block_kernel(const __grid_constant__ CUtensorMap tmQK, const __grid_con
     mbar_init(bar_qk, 1); mbar_init(bar_dv, 1); mbar_init(bar_mn, 1);
     mbar_init(bar_s, 1); mbar_init(bar_a, 1); mbar_init(bar_b, 1);
     fence_barrier_init();
+    pdl_wait();                                   // qkv / dO come from the previous kernels
     mbar_arrive_expect_tx(bar_qk, 2 * OPB);
     load_tile<T>(sQ, &tmQK, bar_qk, 0, h, b);
     load_tile<T>(sK, &tmQK, bar_qk, 0, a.heads + h, b);
@@ -359,6 +364,7 @@ attn_bwd_block_kernel(const __grid_constant__ CUtensorMap tmQK, const __grid_con
     }
   }
   if (warp == 1) tmem_alloc<512>(tmem_slot);
+  pdl_wait();
   if (t >= 128 && t < 256) {       // mask of key i, lse of query i
     const int i = t - 128;
     float mv = -3.0e38f, lse = 3.0e38f;

@@ -4,6 +4,7 @@
 #include <atomic>
 #include <cstdarg>
 #include <cstdio>
+#include <cstdlib>
 
 namespace b200 {
 
@@ -38,6 +39,45 @@ inline int cuda_fail(cudaError_t e, const char* what) {
     cudaError_t _e = cudaGetLastError();                             \
     if (_e != cudaSuccess) return ::b200::cuda_fail(_e, name);       \
   } while (0)
+
+// Programmatic dependent launch: a kernel launched through launch_pdl may be scheduled while its predecessor on
+// the stream is still draining; it must execute pdl_wait() (vec_utils.cuh) before touching memory the predecessor
+// produces.  Kernels call pdl_trigger() first thing so that THEIR successor can be scheduled early.  Hides launch
+// latency and per-kernel prologues (barrier init, TMEM allocation, descriptor prefetch) behind the previous tail.
+// Opt-in (B200_PDL=1): measured on B200 it removes ~0.7 us per kernel boundary inside a captured graph (attention
+// forward 25.6 -> 25.0 us back to back) but the whole training step does not move (8.616 vs 8.598 ms), so the
+// default stays with ordinary stream-ordered launches.
+inline bool pdl_enabled() {
+  static const bool on = [] { const char* e = getenv("B200_PDL"); return e && e[0] == '1'; }();
+  return on;
+}
+
+template <typename... KArgs, typename... Args>
+inline cudaError_t launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t stream,
+                              int cluster_x, Args&&... args) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = grid;
+  cfg.blockDim = block;
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = stream;
+  cudaLaunchAttribute attr[2];
+  unsigned n = 0;
+  if (pdl_enabled()) {
+    attr[n].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[n].val.programmaticStreamSerializationAllowed = 1;
+    ++n;
+  }
+  if (cluster_x > 1) {
+    attr[n].id = cudaLaunchAttributeClusterDimension;
+    attr[n].val.clusterDim.x = cluster_x;
+    attr[n].val.clusterDim.y = 1;
+    attr[n].val.clusterDim.z = 1;
+    ++n;
+  }
+  cfg.attrs = attr;
+  cfg.numAttrs = n;
+  return cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...);
+}
 
 inline int num_sms() {
   static int n = 0;

@@ -448,6 +448,8 @@ colsum_partial_kernel(const T* __restrict__ x, long long ldx, int rows, int cols
 template <typename T>
 __global__ void __launch_bounds__(256)
 colsum_atomic_kernel(const T* __restrict__ x, long long ldx, int rows, int cols, int rows_per_block, float* __restrict__ out) {
+  pdl_trigger();
+  pdl_wait();
   __shared__ float4 red[8][32];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int c = blockIdx.x * 128 + lane * 4;
@@ -671,7 +673,7 @@ extern "C" int b200_colsum(int dtype, const void* x, long long ldx, int rows, in
     if ((reinterpret_cast<uintptr_t>(out) & 15) != 0) return fail(B200_ERR_ARG, "colsum: out must be 16-byte aligned");
     const int rpb0 = (rows + parts - 1) / parts;
     dim3 grid0((cols + 127) / 128, parts);
-    DISPATCH_T(dtype, (colsum_atomic_kernel<T><<<grid0, 256, 0, (cudaStream_t)stream>>>((const T*)x, ldx, rows, cols, rpb0, out)));
+    DISPATCH_T(dtype, (launch_pdl(colsum_atomic_kernel<T>, grid0, dim3(256), 0, (cudaStream_t)stream, 1, (const T*)x, ldx, rows, cols, rpb0, out)));
     B200_LAUNCHED("colsum_atomic_kernel");
     return 0;
   }

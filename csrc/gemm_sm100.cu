@@ -109,6 +109,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
   const uint32_t crank = CTA2 ? cluster_ctarank() : 0u;      // 0 = leader of the pair
+  pdl_trigger();                       // the next kernel on the stream may start its own prologue
 
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&tmA);
@@ -135,6 +136,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
   __syncthreads();
   tcgen05_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  pdl_wait();                          // everything above overlapped the previous kernel's tail; its results from here on
 
   // CTA2: args.num_m counts 256-row pair tiles and the pair index replaces blockIdx.x in the tile schedule
   const int num_tiles = args.nbatch * args.num_m * args.num_n * args.splits;
@@ -646,19 +648,7 @@ static int launch_gemm_cta2(const CUtensorMap& tA, const CUtensorMap& tB, const 
   const long long tiles = (long long)args.nbatch * args.num_m * args.num_n * args.splits;     // pair tiles
   const int pairs = num_sms() / 2;
   const int grid = 2 * (int)(tiles < pairs ? tiles : pairs);
-  cudaLaunchConfig_t cfg = {};
-  cfg.gridDim = dim3(grid);
-  cfg.blockDim = dim3(kGemmThreads);
-  cfg.dynamicSmemBytes = smem;
-  cfg.stream = stream;
-  cudaLaunchAttribute attr[1];
-  attr[0].id = cudaLaunchAttributeClusterDimension;
-  attr[0].val.clusterDim.x = 2;
-  attr[0].val.clusterDim.y = 1;
-  attr[0].val.clusterDim.z = 1;
-  cfg.attrs = attr;
-  cfg.numAttrs = 1;
-  B200_CUDA(cudaLaunchKernelEx(&cfg, kern, tA, tB, tD, tD2, tX, args));
+  B200_CUDA(launch_pdl(kern, dim3(grid), dim3(kGemmThreads), smem, stream, 2, tA, tB, tD, tD2, tX, args));
   B200_LAUNCHED("gemm_tcgen05_kernel<cta2>");
   return 0;
 }
@@ -678,7 +668,7 @@ static int launch_gemm(const CUtensorMap& tA, const CUtensorMap& tB, const CUten
       }
       const long long tiles_sm = (long long)args.nbatch * args.num_m * args.num_n * args.splits;
       const int grid_sm = tiles_sm < num_sms() ? (int)tiles_sm : num_sms();
-      kern_sm<<<grid_sm, kGemmThreads, smem, stream>>>(tA, tB, tD, tD2, tX, args);
+      B200_CUDA(launch_pdl(kern_sm, dim3(grid_sm), dim3(kGemmThreads), smem, stream, 1, tA, tB, tD, tD2, tX, args));
       B200_LAUNCHED("gemm_tcgen05_kernel<softmax>");
       return 0;
     }
@@ -692,7 +682,7 @@ static int launch_gemm(const CUtensorMap& tA, const CUtensorMap& tB, const CUten
   }
   const long long tiles = (long long)args.nbatch * args.num_m * args.num_n * args.splits;
   const int grid = tiles < num_sms() ? (int)tiles : num_sms();
-  kern<<<grid, kGemmThreads, smem, stream>>>(tA, tB, tD, tD2, tX, args);
+  B200_CUDA(launch_pdl(kern, dim3(grid), dim3(kGemmThreads), smem, stream, 1, tA, tB, tD, tD2, tX, args));
   B200_LAUNCHED("gemm_tcgen05_kernel");
   return 0;
 }

@@ -61,6 +61,8 @@ template <typename T, int NV>
 __global__ void __launch_bounds__(kLnThreads)
 ln_fwd_kernel(const LnCommon<T> a, T* __restrict__ y, long long ldy, float* __restrict__ mean_out,
               float* __restrict__ rstd_out) {
+  pdl_trigger();
+  pdl_wait();
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const unsigned long long seed = a.seed_dev ? *a.seed_dev : 0ull;
   const Philox ph(seed);
@@ -203,6 +205,8 @@ __global__ void __launch_bounds__(kLnThreads, 2)
 ln_bwd2_kernel(const LnCommon<T> a, const T* __restrict__ dy, long long lddy, const float* __restrict__ mean_in,
                const float* __restrict__ rstd_in, T* __restrict__ ds, long long ldds, T* __restrict__ dz, long long lddz,
                float* __restrict__ scratch, int want_dbias, const LnDirect direct) {
+  pdl_trigger();
+  pdl_wait();
   extern __shared__ float red[];            // [4 row-slots][cols] for the final fold
   __shared__ float2 part[2][4][2];          // [parity][row slot][half]
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -358,9 +362,9 @@ static int ln_fwd_t(const b200_ln_args* a, cudaStream_t st) {
   int blocks = (a->rows + kLnWarps - 1) / kLnWarps;
   const int cap = num_sms() * 8;
   if (blocks > cap) blocks = cap;
-  if (a->cols <= 256) ln_fwd_kernel<T, 2><<<blocks, kLnThreads, 0, st>>>(c, (T*)a->y, a->ldy, a->mean, a->rstd);
-  else if (a->cols <= 768) ln_fwd_kernel<T, 6><<<blocks, kLnThreads, 0, st>>>(c, (T*)a->y, a->ldy, a->mean, a->rstd);
-  else ln_fwd_kernel<T, 8><<<blocks, kLnThreads, 0, st>>>(c, (T*)a->y, a->ldy, a->mean, a->rstd);
+  if (a->cols <= 256) launch_pdl(ln_fwd_kernel<T, 2>, dim3(blocks), dim3(kLnThreads), 0, st, 1, c, (T*)a->y, a->ldy, a->mean, a->rstd);
+  else if (a->cols <= 768) launch_pdl(ln_fwd_kernel<T, 6>, dim3(blocks), dim3(kLnThreads), 0, st, 1, c, (T*)a->y, a->ldy, a->mean, a->rstd);
+  else launch_pdl(ln_fwd_kernel<T, 8>, dim3(blocks), dim3(kLnThreads), 0, st, 1, c, (T*)a->y, a->ldy, a->mean, a->rstd);
   B200_LAUNCHED("ln_fwd_kernel");
   return 0;
 }
@@ -384,8 +388,8 @@ static int ln_bwd_t(const b200_ln_args* a, cudaStream_t st) {
     const bool direct_mode = a->scratch == nullptr;
     const LnDirect direct{a->dgamma, a->dbeta, a->dbias};
 #define LN_BWD2(NVH)                                                                                                  \
-  ln_bwd2_kernel<T, NVH><<<blocks, kLnThreads, smem2, st>>>(c, (const T*)a->dy, a->lddy, a->mean, a->rstd, (T*)a->ds,  \
-                                                            a->ldds, (T*)a->dz, a->lddz, (float*)a->scratch, want, direct)
+  launch_pdl(ln_bwd2_kernel<T, NVH>, dim3(blocks), dim3(kLnThreads), smem2, st, 1, c, (const T*)a->dy, a->lddy, a->mean,  \
+             a->rstd, (T*)a->ds, a->ldds, (T*)a->dz, a->lddz, (float*)a->scratch, want, direct)
     switch (a->cols / 256) {
       case 1: LN_BWD2(1); break;
       case 2: LN_BWD2(2); break;

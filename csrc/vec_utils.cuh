@@ -7,6 +7,11 @@
 
 namespace b200 {
 
+// programmatic dependent launch (see launch_pdl in common.h); both are no-ops for ordinary launches
+__device__ __forceinline__ void pdl_trigger() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+
+
 struct f4 {
   float x, y, z, w;
 };

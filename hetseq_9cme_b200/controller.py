@@ -105,7 +105,11 @@ class Controller:
         self._graph = None
         self._g_raw = None
         self._graph_sig = None
-        self._graph_seen = 0
+        self._graph_cache: Dict[Any, Dict[str, Any]] = {}     # batch signature -> captured step
+        self._graph_seen_by_sig: Dict[Any, int] = {}
+        self._graph_steps_total = 0
+        self._graph_pool = None
+        self._g_hyper = None
         self.init_meters(args)
 
     # ------------------------------------------------------------------------------------------------
@@ -444,15 +448,21 @@ class Controller:
             return False
         if type(self._reducer).__name__ == "TorchReducer":
             return False
-        if not isinstance(samples[0], (list, tuple)):
+        if not isinstance(samples[0], (list, tuple, dict)):
             return False
         sig = self._sig(samples[0])
-        if self._graph is not None:
-            return sig == self._graph_sig
-        if sig != self._graph_sig:
-            self._graph_sig, self._graph_seen = sig, 0
-        self._graph_seen += 1
-        return self._graph_seen > 3          # a few eager steps first (lazy initialisation, warm caches)
+        if sig in self._graph_cache:
+            return True
+        # a few eager steps first (lazy initialisation, warm caches); later shapes are captured on their second visit.
+        # Batches padded to the longest sequence (NER) produce one graph per distinct length, up to MAX_GRAPHS.
+        seen = self._graph_seen_by_sig.get(sig, 0) + 1
+        self._graph_seen_by_sig[sig] = seen
+        self._graph_steps_total += 1
+        if len(self._graph_cache) >= self.MAX_GRAPHS:
+            return False
+        return self._graph_steps_total > 3 and (seen > 1 or not self._graph_cache)
+
+    MAX_GRAPHS = 24
 
     def _graph_body(self):
         """One full step on the static buffers (runs eagerly while capturing)."""
@@ -486,17 +496,22 @@ class Controller:
     def _graph_capture(self, sample):
         dev = self.device
         from .data.packed import PackedBertBatch
+        sig = self._sig(sample)
         self._g_raw = None
         if isinstance(sample, PackedBertBatch):
             from .ops import kernels as _k
             self._g_raw, self._g_raw_dims = sample.raw.to(dev).clone(), sample.dims
             self._g_sample = _k.assemble_bert_batch(self._g_raw, *self._g_raw_dims)
             sample = self._g_sample
+        elif isinstance(sample, dict):
+            self._g_sample = {k: (v.to(dev).clone() if torch.is_tensor(v) else v) for k, v in sample.items()}
         else:
             self._g_sample = [t.to(dev).clone() for t in sample]
-        self._g_hyper = torch.zeros(4, dtype=torch.float32, device=dev)
-        self._g_hyper_host = torch.zeros(4, dtype=torch.float32).pin_memory()
-        self._g_out = torch.zeros(self._mailbox.FIELDS, dtype=torch.float64, device=dev)
+        if self._g_hyper is None:           # shared by every captured shape
+            self._g_hyper = torch.zeros(4, dtype=torch.float32, device=dev)
+            self._g_hyper_host = torch.zeros(4, dtype=torch.float32).pin_memory()
+            self._g_out = torch.zeros(self._mailbox.FIELDS, dtype=torch.float64, device=dev)
+            self._graph_pool = torch.cuda.graph_pool_handle()
         ss = self.task._sample_size(sample)
         ntok = self.task._num_tokens(sample)
         self._g_const = torch.tensor([float(ss), float(ss), float(ntok)], dtype=torch.float32, device=dev)
@@ -508,13 +523,18 @@ class Controller:
         g = torch.cuda.CUDAGraph()
         self._model.train()
         before = native.launch_count()
-        with torch.cuda.graph(g):
+        with torch.cuda.graph(g, pool=self._graph_pool):      # replays are serial, so all shapes share one pool
             self._graph_body()
         self._graph_launches = native.launch_count() - before      # kernels of ours inside one replay
         native.add_launch_count(-self._graph_launches)              # capture recorded them, it did not run them
         self._graph = g
+        self._graph_sig = sig
+        self._graph_cache[sig] = {"graph": g, "sample": self._g_sample, "raw": self._g_raw,
+                                  "raw_dims": getattr(self, "_g_raw_dims", None), "const": self._g_const,
+                                  "launches": self._graph_launches}
         self._settle_gc(again=True)
-        print("| captured the training step in a CUDA graph ({} tensors, sample size {})".format(len(sample), ss))
+        print("| captured the training step in a CUDA graph (#{}: {} tensors, sample size {})".format(
+            len(self._graph_cache), len(sample), ss))
 
     def _stage_hyper(self):
         opt = self.optimizer.optimizer
@@ -526,10 +546,19 @@ class Controller:
     def _graph_train_step(self, sample):
         self.meters["train_wall"].start()
         self._set_seed()
-        if self._graph is None:
+        sig = self._sig(sample)
+        st = self._graph_cache.get(sig)
+        if st is None:
             self._graph_capture(sample)
+        elif sig != self._graph_sig:         # switch to the graph captured for this batch shape
+            self._graph, self._g_sample, self._g_raw, self._g_raw_dims = st["graph"], st["sample"], st["raw"], st["raw_dims"]
+            self._g_const, self._graph_launches, self._graph_sig = st["const"], st["launches"], sig
         if self._g_raw is not None:
             self._g_raw.copy_(sample[0], non_blocking=True)
+        elif isinstance(sample, dict):
+            for k, src in sample.items():
+                if torch.is_tensor(src):
+                    self._g_sample[k].copy_(src, non_blocking=True)
         else:
             for dst, src in zip(self._g_sample, sample):
                 dst.copy_(src, non_blocking=True)

@@ -196,6 +196,10 @@ _ENGINE = [
     (("--no-native",), dict(action="store_true", help="force the plain-PyTorch model path (CPU/debug only)")),
     (("--cuda-graph",), dict(action="store_true", help="capture the fixed-shape train step in a CUDA graph")),
     (("--checkpoint-activations",), dict(action="store_true", help="recompute encoder activations in backward")),
+    (("--pad-to-multiple-of",), dict(type=int, default=0, metavar="N",
+                                     help="NER / EL collators: pad the batch width up to a multiple of N (0: longest "
+                                          "sequence, as the reference); with --cuda-graph this bounds the number of "
+                                          "distinct batch shapes, i.e. of captured graphs")),
     (("--device-batch-assembly",), dict(action="store_true",
                                         help="ship BERT batches as one packed int32 matrix and build the int64 inputs / "
                                              "dense MLM labels with a kernel on the GPU")),

@@ -25,7 +25,8 @@ class BertForELClassificationTask(BertForTokenClassificationTask):
     @classmethod
     def setup_task(cls, args, **kwargs):
         tokenizer = conll.build_tokenizer(args.dict, getattr(args, "max_pred_length", 512))
-        collator = cls.collator_cls(tokenizer, max_length=getattr(args, "max_pred_length", 512), padding=True)
+        collator = cls.collator_cls(tokenizer, max_length=getattr(args, "max_pred_length", 512), padding=True,
+                                    pad_to_multiple_of=(getattr(args, "pad_to_multiple_of", 0) or None))
         ent_vecs = torch.load(args.ent_vecs_filename, map_location="cpu", weights_only=False)
         ent_vecs = torch.as_tensor(ent_vecs).float()
         vocab_path = os.path.join(os.path.dirname(args.ent_vecs_filename), "entity_vocab.txt")

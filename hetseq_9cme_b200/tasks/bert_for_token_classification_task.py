@@ -53,7 +53,8 @@ class BertForTokenClassificationTask(Task):
     @classmethod
     def setup_task(cls, args, **kwargs):
         tokenizer = conll.build_tokenizer(args.dict, getattr(args, "max_pred_length", 512))
-        collator = cls.collator_cls(tokenizer, max_length=getattr(args, "max_pred_length", 512), padding=True)
+        collator = cls.collator_cls(tokenizer, max_length=getattr(args, "max_pred_length", 512), padding=True,
+                                    pad_to_multiple_of=(getattr(args, "pad_to_multiple_of", 0) or None))
         splits, label_list = cls._read_splits(args)
         label_to_id = {l: i for i, l in enumerate(label_list)}
         tokenized = {k: conll.tokenize_and_align(tokenizer, v, label_to_id, getattr(args, "max_pred_length", 512))

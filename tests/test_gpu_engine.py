@@ -110,3 +110,45 @@ def test_device_batch_assembly_kernel_and_step(tmp_path):
     for other in (packed, graph):
         assert (a - other.arena.master).abs().max().item() <= 2e-4 * a.abs().max().item()
     assert abs(plain.get_meter("train_loss").avg - packed.get_meter("train_loss").avg) < 1e-3
+
+
+def test_cuda_graph_cache_handles_several_batch_shapes(tmp_path):
+    """NER batches are padded to the longest sentence: with --cuda-graph every distinct width gets its own captured
+    step (shared memory pool), and the run must match the eager one."""
+    from hetseq_9cme_b200 import options, tasks
+    from hetseq_9cme_b200.controller import Controller
+    from hetseq_9cme_b200.data import synthetic
+    d = str(tmp_path)
+    paths = synthetic.make_conll(d, n_train=400, n_valid=8, n_test=8, vocab_words=300, seed=3)
+    cfg = synthetic.write_bert_config(d + "/c.json", vocab_size=305, **CFG)
+
+    def build(extra):
+        argv = ["--task", "BertForTokenClassification", "--optimizer", "adam", "--data", d, "--dict", paths["vocab"],
+                "--config_file", cfg, "--train_file", paths["train"], "--validation_file", paths["validation"],
+                "--test_file", paths["test"], "--max-sentences", "8", "--lr", "1e-3", "--warmup-updates", "2",
+                "--total-num-update", "100", "--clip-norm", "1.0", "--valid-subset", "test", "--save-dir", d + "/ck",
+                "--distributed-world-size", "1", "--num-workers", "0", "--log-format", "none", "--fast-stat-sync", "--seed", "7",
+                "--pad-to-multiple-of", "8"] + extra
+        args = options.parse_training_args(argv)
+        torch.manual_seed(0)
+        task = tasks.TASK_REGISTRY["BertForTokenClassification"].setup_task(args)
+        task.load_dataset("test")
+        c = Controller(args, task, task.build_model(args))
+        it = c.get_train_iterator(epoch=0, load_dataset=True)
+        c.lr_step(it.epoch)
+        return c, it.next_epoch_itr(shuffle=False)
+
+    eager, it1 = build([])
+    graph, it2 = build(["--cuda-graph"])
+    widths = set()
+    for _ in range(30):
+        s1, s2 = next(it1), next(it2)
+        widths.add(int(s2["input_ids"].shape[1]))
+        eager.train_step([s1]); graph.train_step([s2])
+    eager.flush_stats(); graph.flush_stats()
+    assert len(widths) >= 2 and all(w % 8 == 0 for w in widths)
+    assert 2 <= len(graph._graph_cache) <= len(widths)
+    assert eager.get_num_updates() == graph.get_num_updates() == 30
+    a, b = eager.arena.master, graph.arena.master
+    assert (a - b).abs().max().item() <= 5e-4 * a.abs().max().item()
+    assert abs(eager.get_meter("train_loss").avg - graph.get_meter("train_loss").avg) < 2e-3

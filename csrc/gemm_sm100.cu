@@ -54,12 +54,22 @@ constexpr int kGemmThreads = 192;
 constexpr int kStageBufBytes = 4096;  // 32 rows x 128 B
 constexpr int kEpiBytes = 4 * 2 * kStageBufBytes;
 
-__device__ __forceinline__ float gelu_f(float x) { return 0.5f * x * (1.0f + erff(x * 0.70710678118654752f)); }
-__device__ __forceinline__ float dgelu_f(float x) {
-  const float cdf = 0.5f * (1.0f + erff(x * 0.70710678118654752f));
-  const float pdf = 0.3989422804014327f * __expf(-0.5f * x * x);
-  return cdf + x * pdf;
+// erf-GELU and its derivative from ONE exponential: with z = x / sqrt(2), exp(-z^2) = exp(-x^2 / 2) serves both the
+// Abramowitz-Stegun 7.1.26 rational form of erf(z) (|error| <= 1.5e-7, far below TF32 / bf16 rounding) and the normal
+// density.  The epilogue warps are issue-bound (one warp per scheduler), so instructions per element are what counts:
+// erff() + __expf() cost roughly twice this.
+__device__ __forceinline__ void gelu_pair(float x, float& g, float& dg) {
+  const float e = __expf(-0.5f * x * x);
+  const float az = fabsf(x) * 0.70710678118654752f;
+  const float t = __fdividef(1.0f, fmaf(0.3275911f, az, 1.0f));
+  const float poly = t * fmaf(t, fmaf(t, fmaf(t, fmaf(t, 1.061405429f, -1.453152027f), 1.421413741f), -0.284496736f), 0.254829592f);
+  const float erf_abs = fmaf(-poly, e, 1.0f);                    // erf(|z|)
+  const float cdf = 0.5f * (1.0f + copysignf(erf_abs, x));
+  g = x * cdf;
+  dg = fmaf(x * 0.3989422804014327f, e, cdf);
 }
+__device__ __forceinline__ float gelu_f(float x) { float g, dg; gelu_pair(x, g, dg); return g; }
+__device__ __forceinline__ float dgelu_f(float x) { float g, dg; gelu_pair(x, g, dg); return dg; }
 
 template <typename T>
 __device__ __forceinline__ float to_f(T v);
@@ -459,7 +469,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
           }
         }
 
-        auto stage_and_store = [&](const CUtensorMap* tm, bool reduce) {
+        auto stage_and_store = [&](const CUtensorMap* tm, bool reduce, const float (&v)[CW]) {
           uint8_t* buf = stg + (ev & 1) * kStageBufBytes;
           if (lane == 0) tma_store_wait_read<1>();   // the store that last used this buffer has drained
           __syncwarp();
@@ -494,7 +504,14 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
           ++ev;
         };
 
-        if (args.has_d2) stage_and_store(&tmD2, false);
+        if (args.act == B200_ACT_GELU_SAVE_GRAD) {
+          float dv[CW];                                  // D2 = gelu'(x) for the backward pass, D = gelu(x)
+#pragma unroll
+          for (int j = 0; j < CW; ++j) gelu_pair(v[j], v[j], dv[j]);
+          stage_and_store(&tmD2, false, dv);
+        } else if (args.has_d2) {
+          stage_and_store(&tmD2, false, v);
+        }
 
         if (args.act == B200_ACT_GELU) {
 #pragma unroll
@@ -516,6 +533,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
               const float x = to_f<TOut>(a[e]);
               const int j = i * (16 / OS) + e;
               if (args.aux_mode == B200_AUX_ADD) v[j] += x;
+              else if (args.aux_mode == B200_AUX_MUL) v[j] *= x;
               else if (args.aux_mode == B200_AUX_MUL_DGELU) v[j] *= dgelu_f(x);
               else v[j] *= (1.0f - x * x);
             }
@@ -534,13 +552,14 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
               for (int e = 0; e < 16 / OS; ++e) {
                 const float x = to_f<TOut>(a[e]);
                 if (args.aux_mode == B200_AUX_ADD) v[j + e] += x;
+                else if (args.aux_mode == B200_AUX_MUL) v[j + e] *= x;
                 else if (args.aux_mode == B200_AUX_MUL_DGELU) v[j + e] *= dgelu_f(x);
                 else v[j + e] *= (1.0f - x * x);
               }
             }
           }
         }
-        stage_and_store(&tmD, args.accumulate != 0);
+        stage_and_store(&tmD, args.accumulate != 0, v);
       }
       // all TMEM reads of this accumulator slot are done -> hand it back to the MMA warp
       tcgen05_fence_before();
@@ -750,14 +769,15 @@ static int choose_bn(int M, int N, int splits, int nbatch) {
 // Does the CTA-pair kernel pay for this problem?  It halves the B traffic per SM but schedules 256-row tiles on 74
 // pairs.  Measured on B200 (profiles/README.md §9): 8-18 % faster on 8192^3 (except fp32 with MN-major A: 17 % slower),
 // 4-7 % on [4096 x 3072 x 768], nothing on the narrower BERT-base GEMMs, and a BERT-base training step with it forced
-// everywhere is 1.3 % SLOWER (coarser tiles with < 3 waves), a BERT-large step 0.5 % faster.  Hence: large problems only.
+// everywhere is 1.3 % SLOWER (coarser tiles with < 3 waves), a BERT-large step 0.5 % faster.  Hence: >= 3 waves only
+// (in BERT-base that is the two [4096 x 3072 x 768] GEMMs: 35.2 -> 33.7 us and 39.1 -> 36.3 us).
 static bool cta2_pays(int M, int N, int bn, int splits, int nbatch, bool fp32_a_mn) {
   if (fp32_a_mn) return false;
   const int sms = num_sms();
   const long long t1 = (long long)((M + 127) / 128) * ((N + bn - 1) / bn) * splits * nbatch;
   const long long t2 = (long long)((M + 255) / 256) * ((N + bn - 1) / bn) * splits * nbatch;
   const long long w1 = (t1 + sms - 1) / sms, w2 = (t2 + sms / 2 - 1) / (sms / 2);
-  return w2 <= w1 && w2 >= 4;
+  return w2 <= w1 && w2 >= 3;
 }
 
 static int gemm_impl(const b200_gemm_desc* d, cudaStream_t stream) {
@@ -773,6 +793,7 @@ static int gemm_impl(const b200_gemm_desc* d, cudaStream_t stream) {
     if ((d->N % (16 / os)) != 0 || ((d->ldaux * os) & 15) != 0 || (reinterpret_cast<uintptr_t>(d->aux) & 15))
       return fail(B200_ERR_ARG, "gemm: aux needs N and pitch multiple of 16 bytes and an aligned base");
   }
+  if (d->act == B200_ACT_GELU_SAVE_GRAD && !d->D2) return fail(B200_ERR_ARG, "gemm: GELU_SAVE_GRAD needs D2 for the derivative");
   if (d->bias && (d->N % (16 / os)) == 0 && (reinterpret_cast<uintptr_t>(d->bias) & 15))
     return fail(B200_ERR_ARG, "gemm: bias must be 16-byte aligned");
 
@@ -801,8 +822,13 @@ static int gemm_impl(const b200_gemm_desc* d, cudaStream_t stream) {
           const long long tiles = base * sp;
           const long long waves = (tiles + num_sms() - 1) / num_sms();
           const int kbs = (kb_total + sp - 1) / sp;
-          const double width = bn == 64 ? 96.0 : (double)bn;
-          const double cost = (double)waves * ((double)kbs * width + 6.0 * bn + 400.0);
+          // cycles per k-block: the slower of the tensor core (~2.87 cycles per output column at the sustained
+          // rate) and operand ingest ((128 + bn) rows of 128 B at ~60 B/clk per SM); wide tiles amortise the A
+          // tile, which is why 256 x split-2 beats 128 x split-1 by 26 % on the FFN weight gradients
+          // (tools/gpu_sweep_wgrad.py, profiles/README.md §10).  Plus the per-tile epilogue (TMEM -> TMA reduce-add).
+          const double mma = 2.87 * (bn == 64 ? 96.0 : (double)bn);
+          const double ingest = 2.15 * (128.0 + bn);
+          const double cost = (double)waves * ((double)kbs * (mma > ingest ? mma : ingest) + 5.0 * bn + 800.0);
           if (cost < best - 1e-9) { best = cost; splits = sp; joint_bn = bn; }
         }
       }

@@ -175,7 +175,8 @@ def _layer_forward(x, nctx, lp, attn_mask, B, L, sid, p_attn, p_hid):
     y1, mean1, rstd1 = K.ln_fwd(z1, lp.g1, lp.be1, bias=lp.bo, residual=x, eps=lp.eps, p_pre=p_hid, seed=nctx.seed,
                                 stream_pre=sid + 2)
     u = torch.empty((B * L, lp.W1.shape[0]), dtype=dt, device=dev)
-    a = gemm(y1, lp.W1, bias=lp.b1, act=N.ACT_GELU, preact_out=u)
+    # u receives gelu'(pre-activation) straight from the epilogue that computes gelu: backward only multiplies
+    a = gemm(y1, lp.W1, bias=lp.b1, act=N.ACT_GELU_SAVE_GRAD, preact_out=u)
     z2 = gemm(a, lp.W2)
     y2, mean2, rstd2 = K.ln_fwd(z2, lp.g2, lp.be2, bias=lp.b2, residual=y1, eps=lp.eps, p_pre=p_hid, seed=nctx.seed,
                                 stream_pre=sid + 3)
@@ -251,7 +252,7 @@ class BertLayerFn(torch.autograd.Function):
         if dz2 is None:
             dz2 = ds2
         gemm(dz2, a, a_mn=True, b_mn=True, out=_mg(lp.W2), **wg)                                 # dW2 += dz2^T a
-        du = gemm(dz2, lp.W2, b_mn=True, aux=u, aux_mode=N.AUX_MUL_DGELU)                         # (dz2 W2) * gelu'(u)
+        du = gemm(dz2, lp.W2, b_mn=True, aux=u, aux_mode=N.AUX_MUL)                               # (dz2 W2) * gelu'(pre), u = gelu' 
         K.colsum_(du, _mg(lp.b1), ws)
         gemm(du, y1, a_mn=True, b_mn=True, out=_mg(lp.W1), **wg)                                 # dW1 += du^T y1
         dy1 = gemm(du, lp.W1, b_mn=True, aux=ds2, aux_mode=N.AUX_ADD)                             # + residual branch

@@ -37,6 +37,8 @@ def gemm(a: torch.Tensor, b: torch.Tensor, *, a_mn: bool = False, b_mn: bool = F
     a: [M,K] (a_mn=False) or [K,M] (a_mn=True);  b: [N,K] (b_mn=False) or [K,N] (b_mn=True).
     fp32 operands run on kind::tf32, bf16 operands on kind::f16; output dtype defaults to the operand
     dtype (bf16 operands may request fp32 output, used for weight gradients).
+    ``preact_out`` receives the value before the activation — or, with ``act=ACT_GELU_SAVE_GRAD``, gelu'(value), which
+    the backward GEMM then applies with ``aux_mode=AUX_MUL`` instead of evaluating erf / exp again.
     """
     if a.dtype != b.dtype or a.dtype not in _DT:
         raise ValueError(f"gemm: unsupported operand dtypes {a.dtype}/{b.dtype}")

@@ -32,8 +32,8 @@ class NativeError(RuntimeError):
 
 # ---- enums (mirror include/b200seq.h) -------------------------------------------------------------
 F32_TF32, BF16, BF16_F32OUT = 0, 1, 2
-ACT_NONE, ACT_GELU, ACT_TANH = 0, 1, 2
-AUX_NONE, AUX_ADD, AUX_MUL_DGELU, AUX_MUL_DTANH = 0, 1, 2, 3
+ACT_NONE, ACT_GELU, ACT_TANH, ACT_GELU_SAVE_GRAD = 0, 1, 2, 3
+AUX_NONE, AUX_ADD, AUX_MUL_DGELU, AUX_MUL_DTANH, AUX_MUL = 0, 1, 2, 3, 4
 
 
 class GemmDesc(ctypes.Structure):

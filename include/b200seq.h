@@ -31,10 +31,12 @@ void b200_add_launch_count(long long n);
 enum { B200_F32_TF32 = 0, /* fp32 operands fed to kind::tf32, fp32 out */
        B200_BF16 = 1,     /* bf16 operands, bf16 out */
        B200_BF16_F32OUT = 2 /* bf16 operands, fp32 out (weight gradients) */ };
-enum { B200_ACT_NONE = 0, B200_ACT_GELU = 1, B200_ACT_TANH = 2 };
+enum { B200_ACT_NONE = 0, B200_ACT_GELU = 1, B200_ACT_TANH = 2,
+       B200_ACT_GELU_SAVE_GRAD = 3 /* D = gelu(x), D2 = gelu'(x): backward then only multiplies (B200_AUX_MUL) */ };
 enum { B200_AUX_NONE = 0, B200_AUX_ADD = 1, /* D = f(acc) + aux                          */
        B200_AUX_MUL_DGELU = 2,              /* D = acc * gelu'(aux), aux = pre-activation */
-       B200_AUX_MUL_DTANH = 3 /* D = acc * (1 - aux^2), aux = tanh output */ };
+       B200_AUX_MUL_DTANH = 3, /* D = acc * (1 - aux^2), aux = tanh output */
+       B200_AUX_MUL = 4 /* D = acc * aux (aux = a stored activation derivative) */ };
 
 typedef struct {
   int dtype;

@@ -482,3 +482,39 @@ def test_gemm_cta_pair_matches_single_cta(dtype, majors, monkeypatch):
     gemm(dy, x, a_mn=True, b_mn=True, out=acc, out_dtype=torch.float32, accumulate=True)
     torch.cuda.synchronize()
     assert _rel(acc, 1.0 + dy.double().t() @ x.double()) < (2e-3 if dtype == torch.float32 else 1e-2)
+
+
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+def test_gemm_gelu_with_saved_derivative(dtype):
+    """FFN-1 epilogue that emits gelu(x) and gelu'(x) together (one exponential, rational erf) and the backward epilogue
+    that multiplies by the stored derivative, against torch's erf-GELU and autograd."""
+    from hetseq_9cme_b200.ops import native as N
+    from hetseq_9cme_b200.ops.gemm import gemm
+    torch.manual_seed(8)
+    M, H, I = 512, 256, 1024
+    x = torch.randn(M, H, device="cuda").to(dtype)
+    w = (torch.randn(I, H, device="cuda") * 0.1).to(dtype)
+    b = torch.randn(I, device="cuda").to(dtype)
+    dact = torch.empty(M, I, device="cuda", dtype=dtype)
+    y = gemm(x, w, bias=b, act=N.ACT_GELU_SAVE_GRAD, preact_out=dact)
+    pre = (x.double() @ w.double().t() + b.double()).requires_grad_(True)
+    ref = torch.nn.functional.gelu(pre)
+    g = torch.randn(M, I, device="cuda", dtype=torch.float64)
+    ref.backward(g)
+    tol = 2e-3 if dtype == torch.float32 else 2e-2
+    assert _rel(y, ref.detach()) < tol
+    # gelu'(pre): |gelu''| <= 1.13, so the operand rounding of `pre` (TF32: ~2e-3 here) carries over one to one
+    assert (dact.double() - pre.grad / g).abs().max().item() < 3 * tol
+    # backward: (dz W2) * gelu'  with W2 [H, I]
+    dz = torch.randn(M, H, device="cuda").to(dtype)
+    w2 = (torch.randn(H, I, device="cuda") * 0.1).to(dtype)
+    du = gemm(dz, w2, b_mn=True, aux=dact, aux_mode=N.AUX_MUL)
+    want = (dz.double() @ w2.double()) * dact.double()
+    assert _rel(du, want) < tol
+    # the fast erf form itself: absolute error of gelu against torch over a wide range
+    if dtype == torch.float32:
+        xs = torch.linspace(-8, 8, 1024 * 64, device="cuda").view(1024, 64)
+        eye = torch.eye(64, device="cuda")
+        scratch = torch.empty(1024, 64, device="cuda")
+        got = gemm(xs, eye, act=N.ACT_GELU_SAVE_GRAD, preact_out=scratch)
+        assert (got - torch.nn.functional.gelu(xs.double()).float()).abs().max().item() < 4e-3     # tf32 rounding of xs dominates

@@ -50,9 +50,10 @@ struct GemmArgs {
 };
 
 constexpr int kBM = 128;
-constexpr int kGemmThreads = 192;
+constexpr int kGemmThreads = 192;        // 2 + 4 warps
 constexpr int kStageBufBytes = 4096;  // 32 rows x 128 B
 constexpr int kEpiBytes = 4 * 2 * kStageBufBytes;
+constexpr int epi_bytes(int ew) { return ew * 2 * kStageBufBytes; }
 
 // erf-GELU and its derivative from ONE exponential: with z = x / sqrt(2), exp(-z^2) = exp(-x^2 / 2) serves both the
 // Abramowitz-Stegun 7.1.26 rational form of erf(z) (|error| <= 1.5e-7, far below TF32 / bf16 rounding) and the normal
@@ -81,8 +82,13 @@ __device__ __forceinline__ float to_f<__nv_bfloat16>(__nv_bfloat16 v) { return _
 // CTA2: the kernel is launched in clusters of two CTAs that share every tcgen05.mma (cta_group::2, M = 256):
 // CTA r of the pair owns rows m0 + 128 r of the 256 x BN tile and loads only rows r*BN/2 .. of the B tile; the leader
 // (r = 0) owns the smem-full / TMEM-empty barriers and issues the MMAs, commits are multicast to both CTAs.
-template <typename TIn, typename TOut, int BN, bool A_MN, bool B_MN, int STAGES, bool EPI_SOFTMAX, bool CTA2 = false>
-__global__ void __launch_bounds__(kGemmThreads, 1)
+// EW: number of epilogue warps, 4 or 8.  With 8, warps w and w+4 share a TMEM lane quadrant and take alternate column
+// chunks of the tile; every warp keeps its own staging buffers, store ring and aux barriers.  The four-warp epilogue
+// is issue-latency bound as soon as it does more than load-and-store (bias +6 us, GELU +14..25 us, a second output
+// +10 us on the [4096 x 3072 x 768] GEMM, tools/gpu_probe_epilogue.py); two warps per scheduler hide each other's
+// TMEM-load, MUFU and store-drain latencies.
+template <typename TIn, typename TOut, int BN, bool A_MN, bool B_MN, int STAGES, bool EPI_SOFTMAX, bool CTA2 = false, int EW = 4>
+__global__ void __launch_bounds__(64 + 32 * EW, 1)
 gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                     const __grid_constant__ CUtensorMap tmD, const __grid_constant__ CUtensorMap tmD2,
                     const __grid_constant__ CUtensorMap tmAux, const GemmArgs args) {
@@ -94,6 +100,8 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
   constexpr int B_ROWS = CTA2 ? BN / 2 : BN;   // rows of the B tile held by this CTA
   constexpr int B_BYTES = B_ROWS * 128;
   static_assert(!(CTA2 && EPI_SOFTMAX), "softmax epilogues run single-CTA");
+  static_assert(EW == 4 || (EW == 8 && !EPI_SOFTMAX), "4 or 8 epilogue warps; softmax epilogues own whole rows");
+  constexpr int kEpiB = epi_bytes(EW);
   constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
   constexpr int SLAB_BYTES = BK * 128;
   constexpr uint32_t ACC_STRIDE = (BN <= 64) ? 64 : (BN <= 128 ? 128 : 256);
@@ -108,13 +116,13 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   uint8_t* smem_stage = smem;                                  // STAGES * STAGE_BYTES
   uint8_t* smem_epi = smem + STAGES * STAGE_BYTES;             // 4 warps x 2 x 4 KB
-  uint64_t* bars = reinterpret_cast<uint64_t*>(smem_epi + kEpiBytes);
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem_epi + kEpiB);
   uint64_t* full_bar = bars;
   uint64_t* empty_bar = bars + STAGES;
   uint64_t* tmem_full = bars + 2 * STAGES;
   uint64_t* tmem_empty = bars + 2 * STAGES + 2;
-  uint64_t* aux_bar = bars + 2 * STAGES + 4;                   // [4 epilogue warps][2 staging buffers]
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * STAGES + 12);
+  uint64_t* aux_bar = bars + 2 * STAGES + 4;                   // [EW epilogue warps][2 staging buffers]
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * STAGES + 4 + 2 * EW);
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
@@ -131,9 +139,9 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
     }
     for (int a = 0; a < 2; ++a) {
       mbar_init(&tmem_full[a], 1);
-      mbar_init(&tmem_empty[a], CTA2 ? 8 : 4);          // epilogue warps of both CTAs release the leader's slot
+      mbar_init(&tmem_empty[a], CTA2 ? 2 * EW : EW);    // epilogue warps of both CTAs release the leader's slot
     }
-    for (int a = 0; a < 8; ++a) mbar_init(&aux_bar[a], 1);
+    for (int a = 0; a < 2 * EW; ++a) mbar_init(&aux_bar[a], 1);
     fence_barrier_init();
   }
   if constexpr (CTA2) {
@@ -255,7 +263,9 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
     }
   } else {
     // ===================================== epilogue =========================================
-    const int ew = warp - 2;               // staging-buffer owner index 0..3
+    const int ew = warp - 2;               // staging-buffer owner index 0..EW-1
+    constexpr int CSTEP = EW / 4;          // column chunks are dealt round-robin to the warps of a quadrant
+    const int c_first = ew >> 2;
     const int q = warp & 3;                // TMEM lane quarter this warp may read
     uint8_t* stg = smem_epi + ew * 2 * kStageBufBytes;
     uint32_t ev = 0;                       // store-event counter (ring of 2 staging buffers)
@@ -436,10 +446,10 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
         if (lane == 0) mbar_arrive(&tmem_empty[acc]);
         continue;
       }
-      if (tma_aux && lane == 0 && n0 < args.N && m0 + q * 32 < args.M) issue_aux(n0, m0 + q * 32, ev);
+      if (tma_aux && lane == 0 && n0 + c_first * CW < args.N && m0 + q * 32 < args.M) issue_aux(n0 + c_first * CW, m0 + q * 32, ev);
 
 #pragma unroll 1
-      for (int c = 0; c < BN / CW; ++c) {
+      for (int c = c_first; c < BN / CW; c += CSTEP) {
         const int nc = n0 + c * CW;
         if (nc >= args.N || m0 + q * 32 >= args.M) break;   // warp-uniform: nothing of this chunk is in range
         float v[CW];
@@ -539,8 +549,8 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
             }
           }
           __syncwarp();                                           // everyone has consumed the aux tile
-          const int nc_next = nc + CW;
-          if (lane == 0 && c + 1 < BN / CW && nc_next < args.N) issue_aux(nc_next, m0 + q * 32, ev + 1);
+          const int nc_next = nc + CSTEP * CW;
+          if (lane == 0 && c + CSTEP < BN / CW && nc_next < args.N) issue_aux(nc_next, m0 + q * 32, ev + 1);
         } else if (args.aux_mode != B200_AUX_NONE && row < args.M) {
           const TOut* arow = aux + (long long)row * args.ldaux + nc;
 #pragma unroll
@@ -643,42 +653,65 @@ int make_tmap_4d(CUtensorMap* out, const void* ptr, int elem_bytes, bool is_bf16
 // ------------------------------------------------------------------------------------------------
 // host side: dispatch
 // ------------------------------------------------------------------------------------------------
-template <int BN, bool CTA2 = false>
+template <int BN, bool CTA2 = false, int EW = 4>
 constexpr int stages_for() {
-  // 227 KB usable; keep 32 KB for the epilogue staging ring, ~2 KB for alignment slack + barriers.
+  // 227 KB usable; keep 8 KB per epilogue warp for its staging ring, ~2 KB for alignment slack + barriers.
   constexpr int stage = kBM * 128 + (CTA2 ? BN / 2 : BN) * 128;
-  constexpr int avail = 232448 - kEpiBytes - 2048;
+  constexpr int avail = 232448 - epi_bytes(EW) - 2048;
   constexpr int s = avail / stage;
   return s > 8 ? 8 : s;
 }
 
-// CTA-pair variant: clusters of two CTAs, one pair per TPC, 256 x BN tiles (see the kernel's CTA2 comment)
-template <typename TIn, typename TOut, int BN, bool A_MN, bool B_MN>
-static int launch_gemm_cta2(const CUtensorMap& tA, const CUtensorMap& tB, const CUtensorMap& tD, const CUtensorMap& tD2,
-                            const CUtensorMap& tX, const GemmArgs& args, cudaStream_t stream) {
-  constexpr int STAGES = stages_for<BN, true>();
-  constexpr int smem = STAGES * (kBM * 128 + (BN / 2) * 128) + kEpiBytes + 1024 /*align*/ + (2 * STAGES + 12) * 8 + 16;
-  auto kern = gemm_tcgen05_kernel<TIn, TOut, BN, A_MN, B_MN, STAGES, false, true>;
+// One launch of a (CTA2, EW) variant.  CTA2: clusters of two CTAs, one pair per TPC, 256 x BN tiles.
+template <typename TIn, typename TOut, int BN, bool A_MN, bool B_MN, bool CTA2, int EW>
+static int launch_one(const CUtensorMap& tA, const CUtensorMap& tB, const CUtensorMap& tD, const CUtensorMap& tD2,
+                      const CUtensorMap& tX, const GemmArgs& args, cudaStream_t stream) {
+  constexpr int STAGES = stages_for<BN, CTA2, EW>();
+  constexpr int smem = STAGES * (kBM * 128 + (CTA2 ? BN / 2 : BN) * 128) + epi_bytes(EW) + 1024 /*align*/ +
+                       (2 * STAGES + 4 + 2 * EW) * 8 + 16;
+  auto kern = gemm_tcgen05_kernel<TIn, TOut, BN, A_MN, B_MN, STAGES, false, CTA2, EW>;
   static bool attr_set = false;
   if (!attr_set) {
     B200_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
     attr_set = true;
   }
-  const long long tiles = (long long)args.nbatch * args.num_m * args.num_n * args.splits;     // pair tiles
-  const int pairs = num_sms() / 2;
-  const int grid = 2 * (int)(tiles < pairs ? tiles : pairs);
-  B200_CUDA(launch_pdl(kern, dim3(grid), dim3(kGemmThreads), smem, stream, 2, tA, tB, tD, tD2, tX, args));
-  B200_LAUNCHED("gemm_tcgen05_kernel<cta2>");
+  const long long tiles = (long long)args.nbatch * args.num_m * args.num_n * args.splits;     // pair tiles when CTA2
+  const int units = CTA2 ? num_sms() / 2 : num_sms();
+  const int grid = (CTA2 ? 2 : 1) * (int)(tiles < units ? tiles : units);
+  B200_CUDA(launch_pdl(kern, dim3(grid), dim3(64 + 32 * EW), smem, stream, CTA2 ? 2 : 1, tA, tB, tD, tD2, tX, args));
+  B200_LAUNCHED("gemm_tcgen05_kernel");
   return 0;
+}
+
+// Epilogues that do more than load-and-store get eight epilogue warps (see the kernel's EW comment); B200_GEMM_EW=4/8
+// forces one variant.  Only instantiated for K-major A with matching in/out types (forward and data-gradient GEMMs).
+template <typename TIn, typename TOut, bool A_MN>
+static bool wide_epilogue(const GemmArgs& args) {
+  if constexpr (A_MN || sizeof(TIn) != sizeof(TOut)) {
+    return false;
+  } else {
+    const char* e = getenv("B200_GEMM_EW");
+    if (e) return atoi(e) == 8;
+    return args.bias != nullptr || args.act != B200_ACT_NONE || args.aux_mode != B200_AUX_NONE || args.has_d2;
+  }
+}
+
+template <typename TIn, typename TOut, int BN, bool A_MN, bool B_MN>
+static int launch_gemm_cta2(const CUtensorMap& tA, const CUtensorMap& tB, const CUtensorMap& tD, const CUtensorMap& tD2,
+                            const CUtensorMap& tX, const GemmArgs& args, cudaStream_t stream) {
+  if constexpr (!A_MN && sizeof(TIn) == sizeof(TOut)) {
+    if (wide_epilogue<TIn, TOut, A_MN>(args)) return launch_one<TIn, TOut, BN, A_MN, B_MN, true, 8>(tA, tB, tD, tD2, tX, args, stream);
+  }
+  return launch_one<TIn, TOut, BN, A_MN, B_MN, true, 4>(tA, tB, tD, tD2, tX, args, stream);
 }
 
 template <typename TIn, typename TOut, int BN, bool A_MN, bool B_MN>
 static int launch_gemm(const CUtensorMap& tA, const CUtensorMap& tB, const CUtensorMap& tD, const CUtensorMap& tD2,
                        const CUtensorMap& tX, const GemmArgs& args, cudaStream_t stream) {
-  constexpr int STAGES = stages_for<BN>();
-  constexpr int smem = STAGES * (kBM * 128 + BN * 128) + kEpiBytes + 1024 /*align*/ + (2 * STAGES + 12) * 8 + 16;
   if constexpr (!A_MN && !B_MN && sizeof(TIn) == sizeof(TOut)) {
     if (args.epi_mode != 0) {        // attention-softmax epilogue kernels are separate instantiations
+      constexpr int STAGES = stages_for<BN>();
+      constexpr int smem = STAGES * (kBM * 128 + BN * 128) + kEpiBytes + 1024 /*align*/ + (2 * STAGES + 12) * 8 + 16;
       auto kern_sm = gemm_tcgen05_kernel<TIn, TOut, BN, A_MN, B_MN, STAGES, true>;
       static bool attr_set_sm = false;
       if (!attr_set_sm) {
@@ -693,17 +726,10 @@ static int launch_gemm(const CUtensorMap& tA, const CUtensorMap& tB, const CUten
     }
   }
   if (args.epi_mode != 0) return fail(B200_ERR_UNSUPPORTED, "gemm: softmax epilogues need K-major operands and matching in/out dtype");
-  auto kern = gemm_tcgen05_kernel<TIn, TOut, BN, A_MN, B_MN, STAGES, false>;
-  static bool attr_set = false;
-  if (!attr_set) {
-    B200_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
-    attr_set = true;
+  if constexpr (!A_MN && sizeof(TIn) == sizeof(TOut)) {
+    if (wide_epilogue<TIn, TOut, A_MN>(args)) return launch_one<TIn, TOut, BN, A_MN, B_MN, false, 8>(tA, tB, tD, tD2, tX, args, stream);
   }
-  const long long tiles = (long long)args.nbatch * args.num_m * args.num_n * args.splits;
-  const int grid = tiles < num_sms() ? (int)tiles : num_sms();
-  B200_CUDA(launch_pdl(kern, dim3(grid), dim3(kGemmThreads), smem, stream, 1, tA, tB, tD, tD2, tX, args));
-  B200_LAUNCHED("gemm_tcgen05_kernel");
-  return 0;
+  return launch_one<TIn, TOut, BN, A_MN, B_MN, false, 4>(tA, tB, tD, tD2, tX, args, stream);
 }
 
 template <typename TIn, typename TOut, int BN>

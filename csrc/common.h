@@ -90,4 +90,22 @@ inline int num_sms() {
   return n;
 }
 
+// SMs the persistent compute kernels (GEMM) may fill.  Data-parallel runs can leave a few SMs to the gradient
+// reduction kernels that overlap backward (B200_COMPUTE_SMS, set by the reducer or by hand); default: all.
+inline std::atomic<int>& compute_sm_limit() {
+  static std::atomic<int> v{0};
+  return v;
+}
+inline int compute_sms() {
+  int lim = compute_sm_limit().load(std::memory_order_relaxed);
+  if (lim == 0) {
+    const char* e = getenv("B200_COMPUTE_SMS");
+    lim = e ? atoi(e) : -1;
+    if (lim == 0) lim = -1;
+    compute_sm_limit().store(lim, std::memory_order_relaxed);
+  }
+  const int n = num_sms();
+  return (lim > 0 && lim < n) ? lim : n;
+}
+
 }  // namespace b200

@@ -676,7 +676,7 @@ static int launch_one(const CUtensorMap& tA, const CUtensorMap& tB, const CUtens
     attr_set = true;
   }
   const long long tiles = (long long)args.nbatch * args.num_m * args.num_n * args.splits;     // pair tiles when CTA2
-  const int units = CTA2 ? num_sms() / 2 : num_sms();
+  const int units = CTA2 ? compute_sms() / 2 : compute_sms();
   const int grid = (CTA2 ? 2 : 1) * (int)(tiles < units ? tiles : units);
   B200_CUDA(launch_pdl(kern, dim3(grid), dim3(64 + 32 * EW), smem, stream, CTA2 ? 2 : 1, tA, tB, tD, tD2, tX, args));
   B200_LAUNCHED("gemm_tcgen05_kernel");

@@ -79,6 +79,7 @@ class P2PReducer(BaseReducer):
         # CTA width of the launches that overlap backward (see b200_p2p_allreduce: threads * 1000 + blocks)
         self.threads = int(os.environ.get("B200_P2P_THREADS", 512))
         self.no_overlap = bool(os.environ.get("B200_P2P_NO_OVERLAP"))
+        self._dry = bool(os.environ.get("B200_P2P_DRY"))
         # B200_P2P_DEBUG=1: every bucket is also reduced with torch.distributed (NCCL) from a copy taken right before
         # the launch, and compared after the step; the per-bucket epoch counters are checked against the host's count.
         # Not usable under CUDA-graph capture (it synchronises).
@@ -168,6 +169,8 @@ class P2PReducer(BaseReducer):
             ref = self.arena.grad[s:e].clone()
             dist.all_reduce(ref)
             self._debug_refs[bi] = ref
+        if self._dry:                 # experiment: flag protocol and SM occupancy only, no data movement (WRONG results)
+            n = 0
         one_shot = 1 if n * 4 <= ONE_SHOT_BYTES else 0
         mc = self.mc_base if (self.mc_base and n * 4 >= NVLS_MIN_BYTES) else 0
         native.check(self.lib.b200_p2p_allreduce(self.data_ptrs, self.flag_ptrs, self.counter.data_ptr(), self.rank,

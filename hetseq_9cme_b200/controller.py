@@ -133,11 +133,15 @@ class Controller:
         compute_dtype = torch.bfloat16 if self.precision == "bf16" else torch.float32
         params = [p for p in model.parameters() if p.requires_grad]
         groups = model.arena_groups() if hasattr(model, "arena_groups") else None
-        bucket_bytes = int(getattr(self.args, "bucket_cap_mb", 25)) * 1024 * 1024
+        bucket_mb = int(getattr(self.args, "bucket_cap_mb", 25))
         grad_alloc = None
         if self.cuda and self.world_size > 1 and getattr(self.args, "comm", "auto") in ("auto", "p2p"):
             from .parallel.p2p import symmetric_grad_alloc
             grad_alloc = symmetric_grad_alloc          # NVLS-capable memory when the platform offers it
+            # every bucket of the peer-to-peer reducer costs two flag rounds across all ranks plus a launch; measured on
+            # 2 B200 (ms/step): 25 MB 8.52, 50 MB 8.43, 100 MB 8.35, 250 MB 8.47, 500 MB 8.73 (profiles/README.md §1)
+            bucket_mb = int(getattr(self.args, "p2p_bucket_mb", 100) or bucket_mb)
+        bucket_bytes = int(os.environ.get("B200_BUCKET_MB") or bucket_mb) * 1024 * 1024
         self._arena = ParamArena(params, groups=groups, device=self.device, compute_dtype=compute_dtype,
                                  bucket_bytes=bucket_bytes, grad_alloc=grad_alloc)
         self._reducer = build_reducer(self.args, self._arena, self.world_size)

@@ -193,6 +193,9 @@ _ENGINE = [
                                  "fp32: plain PyTorch fp32 (CPU / debugging)")),
     (("--comm",), dict(default="auto", choices=["auto", "p2p", "torch"],
                        help="gradient reduction: hand-written NVLink peer kernels (p2p) or torch.distributed (torch)")),
+    (("--p2p-bucket-mb",), dict(type=int, default=100, metavar="MB",
+                                help="bucket size of the peer-to-peer reducer (--bucket-cap-mb keeps applying to the "
+                                     "torch.distributed reducer); 0: use --bucket-cap-mb")),
     (("--no-native",), dict(action="store_true", help="force the plain-PyTorch model path (CPU/debug only)")),
     (("--cuda-graph",), dict(action="store_true", help="capture the fixed-shape train step in a CUDA graph")),
     (("--checkpoint-activations",), dict(action="store_true", help="recompute encoder activations in backward")),

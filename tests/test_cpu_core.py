@@ -65,6 +65,30 @@ def test_every_shipped_training_command_parses():
     assert parsed >= 10
 
 
+def test_own_launch_scripts_parse_and_cover_the_reference_layouts():
+    """scripts/ (tools/gen_run_scripts.py) must offer every job layout of the reference's STORE_RUN_FILE tree, and every
+    command in it must be accepted by our parser with consistent ranks."""
+    from hetseq_9cme_b200 import options
+    root = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "scripts")
+    for layout in ("node1gpu4", "node2gpu8", "node2gpu8_het", "node4gpu16", "node4gpu16_het", "node8gpu32_het"):
+        assert os.path.exists(os.path.join(root, "Train_mnist", layout, "main.sh")), layout
+        assert os.path.exists(os.path.join(root, "Train_mnist", layout, "eval.sh")), layout
+    n = 0
+    for path in glob.glob(os.path.join(root, "**", "*.sh"), recursive=True):
+        text = open(path).read().replace("\\\n", " ")
+        for line in text.splitlines():
+            if "train.py" not in line or "--task" not in line:
+                continue
+            line = re.sub(r"\$\{[^}]*\{[^}]*\}[^}]*\}|\$\{[^}]*\}", "1", line)      # ${A:-$B/c} and ${A}
+            tail = re.split(r"\s(?:\||>|2>&1|&)\s?", line.split("train.py", 1)[1])[0]
+            args = options.parse_training_args(shlex.split(tail, comments=True))
+            assert args.task in options.TASKS
+            if "--distributed-rank" in tail:
+                assert args.distributed_rank + args.distributed_gpus <= args.distributed_world_size, path
+            n += 1
+    assert n >= 25
+
+
 def test_flag_defaults_match_reference_table():
     from hetseq_9cme_b200 import options
     a = options.parse_training_args(["--task", "bert", "--config_file", "c.json", "--max-sentences", "8"])

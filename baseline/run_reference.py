@@ -42,7 +42,7 @@ def run_reference(a):
     sys.path.insert(0, ROOT)
     import numpy as np
     import torch.distributed as dist
-    from bench import ClockSampler, MODELS, PUBLISHED_SEQ_PER_SEC_PER_GPU
+    from bench import ClockSampler, MODELS, PUBLISHED_SEQ_PER_SEC_PER_GPU, _metric_name, bench_config
     from hetseq_9cme_b200.data import synthetic   # data *generation* only (same arrays as our arm)
 
     rank = int(os.environ.get("RANK", "0"))
@@ -58,7 +58,7 @@ def run_reference(a):
 
     tmp = tempfile.mkdtemp(prefix="refbench_r%d_" % rank)
     try:
-        nsteps_needed = a.steps + a.warmup + 4
+        nsteps_needed = 2 * a.steps + a.warmup + 8       # fp32 pass + TF32 companion pass
         per_rank = nsteps_needed * a.batch
         max_pred = 20 if a.seq_len <= 128 else 80
         n_per_file = (per_rank * world + 1) // 2 + a.batch
@@ -97,39 +97,60 @@ def run_reference(a):
                 dist.barrier()
                 torch.cuda.synchronize()
 
-        for _ in range(a.warmup):
-            controller.train_step(next(itr))
-        sync_all()
+        def measure(nwarm):
+            """K public-API steps (H2D copies and the reference's own host syncs included); device- and wall-timed."""
+            for _ in range(nwarm):
+                controller.train_step(next(itr))
+            sync_all()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            h2d = 0
+            t0 = time.perf_counter()
+            e0.record()
+            for _ in range(a.steps):
+                samples = next(itr)
+                h2d += sum(t.numel() * t.element_size() for t in samples[0])
+                controller.train_step(samples)
+            e1.record()
+            sync_all()
+            wall_ms = (time.perf_counter() - t0) * 1e3
+            t = torch.tensor([e0.elapsed_time(e1), wall_ms], device="cuda", dtype=torch.float64)
+            if world > 1:
+                dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            return t.tolist() + [h2d]
+
+        # headline: the reference exactly as it ships (torch default: fp32 matmuls on the FP32 pipe)
         sampler = ClockSampler(local)
         sampler.start()
-        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        h2d = 0
-        t0 = time.perf_counter()
-        e0.record()
-        for _ in range(a.steps):
-            samples = next(itr)
-            h2d += sum(t.numel() * t.element_size() for t in samples[0])
-            controller.train_step(samples)
-        e1.record()
-        sync_all()
-        wall_ms = (time.perf_counter() - t0) * 1e3
-        dev_ms = e0.elapsed_time(e1)
+        dev_ms, wall_ms, h2d = measure(a.warmup)
         clocks = sampler.stop()
-        t = torch.tensor([dev_ms, wall_ms], device="cuda", dtype=torch.float64)
-        if world > 1:
-            dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        dev_ms, wall_ms = t.tolist()
+        loss_meter = controller.get_meter("train_loss")
+        final_loss = float(loss_meter.avg) if loss_meter is not None else None
+        # companion datum: same code, cuBLAS allowed to use TF32 tensor cores (a torch switch in this harness, nothing
+        # in baseline/_ref is touched) — the like-for-like partner of our TF32 arm
+        tf32 = None
+        if getattr(a, "precision", "tf32") in ("tf32", "bf16") and True:
+            torch.backends.cuda.matmul.allow_tf32 = True
+            torch.backends.cudnn.allow_tf32 = True
+            try:
+                d2, w2, _ = measure(3)
+                tf32 = {"value": round(a.batch * world * a.steps / (d2 / 1e3), 2), "ms_per_step": round(d2 / a.steps, 4),
+                        "e2e_value": round(a.batch * world * a.steps / (w2 / 1e3), 2), "allow_tf32": True}
+            except StopIteration:
+                tf32 = None
+            torch.backends.cuda.matmul.allow_tf32 = False
+            torch.backends.cudnn.allow_tf32 = False
         gb = a.batch * world
         value = gb * a.steps / (dev_ms / 1e3)
-        out = {"metric": "BERT-base phase-1 pre-training throughput (seq 128)", "value": round(value, 2), "unit": "sequences/s",
+        out = {"metric": _metric_name(a.model, a.seq_len, getattr(a, "task", "bert")), "value": round(value, 2), "unit": "sequences/s",
                "n_gpus": world, "steps": a.steps, "warmup": a.warmup, "ms_per_step": round(dev_ms / a.steps, 4),
                "higher_is_better": True, "scaling": "weak", "vs_baseline": round(value / (PUBLISHED_SEQ_PER_SEC_PER_GPU * world), 2),
                "dtype": "fp32", "data": "synthetic", "impl": "reference",
-               "config": {"model": a.model, "global_batch": gb, "per_gpu_batch": a.batch, "seq_len": a.seq_len,
-                          "parallelism": "dp%d" % world, "allow_tf32": bool(torch.backends.cuda.matmul.allow_tf32),
-                          "path": "hetseq.controller.Controller.train_step (DDP + NCCL + cuBLAS), unmodified",
-                          "timing": "CUDA events around the K public-API steps incl. their H2D copies and host syncs; max over ranks"},
-               "clocks": clocks,
+               "config": bench_config(a, world, max_pred),
+               "impl_detail": {"allow_tf32": False,
+                               "path": "hetseq.controller.Controller.train_step (DDP + NCCL + cuBLAS), unmodified",
+                               "timing": "CUDA events around the K public-API steps incl. their H2D copies and host syncs; max over ranks"},
+               "reference_tf32": tf32,
+               "clocks": clocks, "final_loss": (round(final_loss, 4) if final_loss is not None else None),
                "e2e": {"value": round(gb * a.steps / (wall_ms / 1e3), 2), "unit": "sequences/s",
                        "ms_per_step": round(wall_ms / a.steps, 4), "h2d_bytes_per_step": int(h2d / a.steps),
                        "d2h_bytes_per_step": 48},

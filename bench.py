@@ -44,6 +44,14 @@ def _metric_name(model: str, seq_len: int, task: str = "bert") -> str:
 PUBLISHED_SEQ_PER_SEC_PER_GPU = 12.3   # 49.2 seq/s on 4 GPUs (README.md:65 of the reference)
 
 
+def bench_config(a, world: int, max_pred: int) -> dict:
+    """The workload, in the SAME keys and values for both arms (what differs between them goes to ``impl_detail``)."""
+    return {"model": a.model, "task": a.task, "global_batch": a.batch * world, "per_gpu_batch": a.batch,
+            "seq_len": (a.seq_len if a.task == "bert" else "dynamic (4-40 words per sentence, padded to the longest in the batch)"),
+            "parallelism": "dp%d" % world, "optimizer": "adam", "lr": 1e-4, "weight_decay": 0.01, "clip_norm": 25, "dropout": 0.1,
+            "max_predictions_per_seq": (max_pred if a.task == "bert" else None), "vocab_size": 30522 if a.task == "bert" else 20005}
+
+
 def parse(argv=None):
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -200,8 +208,7 @@ def make_ner_args(a, data_dir, cfg_path, paths, rank, local, world):
             "--fast-stat-sync", "--valid-subset", "test", "--num-workers", "2", "--save-dir", os.path.join(data_dir, "ckpt"),
             "--no-save", "--log-format", "none", "--distributed-world-size", str(world), "--precision", a.precision,
             "--comm", a.comm, "--disable-validation", "--pad-to-multiple-of", "8"]
-    if not a.no_graph:
-        argv.append("--cuda-graph")
+    argv.append("--no-cuda-graph" if a.no_graph else "--cuda-graph")
     args = options.parse_training_args(argv)
     args.distributed_rank = rank
     args.device_id = local
@@ -216,10 +223,8 @@ def make_args(a, data_dir, cfg_path, vocab_path, rank, local, world):
             "--valid-subset", "test", "--num-workers", "2", "--save-dir", os.path.join(data_dir, "ckpt"), "--no-save",
             "--log-format", "none", "--distributed-world-size", str(world), "--precision", a.precision, "--comm", a.comm,
             "--max-predictions-per-seq", "20" if a.seq_len <= 128 else "80", "--disable-validation"]
-    if not a.no_graph:
-        argv.append("--cuda-graph")
-    if not a.no_device_batch:
-        argv.append("--device-batch-assembly")
+    argv.append("--no-cuda-graph" if a.no_graph else "--cuda-graph")
+    argv.append("--no-device-batch-assembly" if a.no_device_batch else "--device-batch-assembly")
     args = options.parse_training_args(argv)
     args.distributed_rank = rank
     args.device_id = local
@@ -363,28 +368,46 @@ def run_ours(a):
             exposed_ms = controller.reducer.exposed_ms()
             controller.reducer.enable_timing(False)
 
+        # ---- replicas must hold identical bits after the timed steps (the multi-GPU tests are skipped on 1-GPU boxes) ----
+        replicas_identical = None
+        if world > 1:
+            params_now = controller.arena.work if controller.arena.work is not None else controller.arena.master
+            chk = params_now.double()
+            v = torch.stack([chk.sum(), chk.pow(2).sum()])
+            v = torch.cat([v, -v])
+            dist.all_reduce(v, op=dist.ReduceOp.MAX)
+            replicas_identical = bool(v[0].item() == -v[2].item() and v[1].item() == -v[3].item())
+
         t = torch.tensor([dev_ms, e2e_ms if not a.no_e2e else 0.0, exposed_ms or 0.0], device="cuda", dtype=torch.float64)
         if world > 1:
             dist.all_reduce(t, op=dist.ReduceOp.MAX)
         dev_ms, e2e_ms, exposed_ms = t.tolist()
         gb = a.batch * world
         value = gb * a.steps / (dev_ms / 1e3)
+        red = controller.reducer
         out = {
             "metric": _metric_name(a.model, a.seq_len, a.task),
             "value": round(value, 2), "unit": "sequences/s", "n_gpus": world, "steps": a.steps, "warmup": a.warmup,
             "ms_per_step": round(dev_ms / a.steps, 4), "higher_is_better": True, "scaling": "weak",
             "vs_baseline": round(value / (PUBLISHED_SEQ_PER_SEC_PER_GPU * world), 2), "dtype": a.precision, "data": "synthetic",
             "impl": "ours",
-            "config": {"model": a.model, "global_batch": gb, "per_gpu_batch": a.batch, "seq_len": (a.seq_len if a.task == "bert" else "dynamic (4-40 words per sentence, padded to the longest in the batch)"), "task": a.task,
-                       "parallelism": "dp%d" % world, "optimizer": "adam (fused, fp32 master)", "dropout": 0.1,
-                       "max_predictions_per_seq": max_pred, "l2_policy": "per-step working set (>= 440 MB) exceeds the 126 MB L2",
-                       "timing": "CUDA events on the training stream, max over ranks", "comm": type(controller.reducer).__name__,
-                       "cuda_graph": bool(controller._graph is not None), "cuda_graphs_captured": len(controller._graph_cache),
-                       "baseline_ref": "12.3 seq/s/GPU published (reference README.md:65, Pascal-era GPUs)"},
+            "config": bench_config(a, world, max_pred),
+            "impl_detail": {"optimizer": "fused Adam on the flat arena, fp32 master" + (
+                                "; sharded: reduce-scatter -> owned-slice update -> parameter broadcast" if getattr(red, "sharded", False) else ""),
+                            "mlm_head": "evaluated at the labelled positions only (identical loss and gradients: ignored targets "
+                                        "contribute nothing; ~18% fewer FLOPs than the reference's full [B*L, vocab] head)",
+                            "l2_policy": "per-step working set (>= 440 MB) exceeds the 126 MB L2",
+                            "timing": "CUDA events on the training stream, max over ranks", "comm": type(red).__name__,
+                            "comm_mapping": getattr(red, "mapping", None), "nvls_multicast": bool(getattr(red, "mc_base", 0)),
+                            "cuda_graph": bool(controller._graph is not None), "cuda_graphs_captured": len(controller._graph_cache),
+                            "baseline_ref": "12.3 seq/s/GPU published (reference README.md:65, Pascal-era GPUs)"},
             "clocks": clocks, "gpu_launches": int(launches), "final_loss": round(float(loss_dev), 4),
             "host_issue_ms_per_step": round(host_issue_ms / a.steps, 3),
             "exposed_allreduce_ms_per_step": (round(exposed_ms, 4) if world > 1 else 0.0),
         }
+        if replicas_identical is not None:
+            out["replicas_identical"] = replicas_identical
+            assert replicas_identical, "data-parallel replicas diverged during the benchmark"
         if not a.no_e2e:
             out["e2e"] = {"value": round(gb * a.steps / (e2e_ms / 1e3), 2), "unit": "sequences/s",
                           "ms_per_step": round(e2e_ms / a.steps, 4), "h2d_bytes_per_step": int(h2d / a.steps),

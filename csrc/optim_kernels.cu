@@ -8,6 +8,7 @@
 // zeroes the gradient for the next step.  No host round trip anywhere.
 #include "common.h"
 #include "vec_utils.cuh"
+#include "optim_math.cuh"
 #include "../include/b200seq.h"
 
 namespace b200 {
@@ -74,50 +75,6 @@ static int sumsq_grid(long long n) {
   if (blocks > kSumsqMaxBlocks) blocks = kSumsqMaxBlocks;
   return (int)blocks;
 }
-
-// ---- derived step scalars -------------------------------------------------------------------------
-struct StepScalars {
-  float scale;   // multiply every gradient by this (grad scale x clip coefficient)
-  float gnorm;   // norm of the scaled, unclipped gradient (what the reference logs as gnorm)
-  float clipped; // 1 if the clip coefficient was applied
-};
-
-__device__ __forceinline__ StepScalars derive_scalars(float mult, const double* sample_size, const float* sample_size_f32,
-                                                      const float* norm_sq, float max_norm) {
-  StepScalars s;
-  float c = mult;
-  if (sample_size != nullptr) {
-    const double ss = *sample_size;
-    c = ss > 0.0 ? (float)((double)mult / ss) : 0.f;
-  } else if (sample_size_f32 != nullptr) {
-    const float ss = *sample_size_f32;
-    c = ss > 0.f ? mult / ss : 0.f;
-  }
-  s.scale = c;
-  s.gnorm = 0.f;
-  s.clipped = 0.f;
-  if (norm_sq != nullptr) {
-    s.gnorm = sqrtf(fmaxf(*norm_sq, 0.f)) * fabsf(c);
-    if (max_norm > 0.f && s.gnorm > max_norm) {
-      // torch.nn.utils.clip_grad_norm_: coef = max_norm / (norm + 1e-6), applied when norm > max_norm
-      s.scale = c * (max_norm / (s.gnorm + 1e-6f));
-      s.clipped = 1.f;
-    }
-  }
-  return s;
-}
-
-struct AdamArgsDev {
-  float lr, beta1, beta2, eps, weight_decay;
-  float step_size;  // lr * sqrt(1-beta2^t) / (1-beta1^t), computed on the host in double
-  float mult, max_norm;
-  const float* norm_sq;
-  const double* sample_size;
-  float* stats_out;
-  int zero_grad;
-  const float* sample_size_f32;
-  const float* hyper_dev;   // optional device float[4]: lr, step_size, (1 - wd*lr), unused — overrides the by-value copies
-};
 
 __global__ void __launch_bounds__(256)
 adam_flat_kernel(float* __restrict__ p, float* __restrict__ g, float* __restrict__ m, float* __restrict__ v,
@@ -259,13 +216,7 @@ extern "C" int b200_adam_flat(float* p, float* g, float* m, float* v, void* p_bf
         reinterpret_cast<uintptr_t>(v)) & 15) != 0)
     return fail(B200_ERR_ARG, "adam: buffers must be 16-byte aligned");
   AdamArgsDev d;
-  d.lr = a->lr; d.beta1 = a->beta1; d.beta2 = a->beta2; d.eps = a->eps; d.weight_decay = a->weight_decay;
-  const double bc1 = 1.0 - pow((double)a->beta1, (double)a->step);
-  const double bc2 = 1.0 - pow((double)a->beta2, (double)a->step);
-  d.step_size = (float)((double)a->lr * sqrt(bc2) / bc1);
-  d.mult = a->grad_scale_mult; d.max_norm = a->max_norm;
-  d.norm_sq = a->norm_sq; d.sample_size = a->sample_size; d.stats_out = a->stats_out; d.zero_grad = a->zero_grad;
-  d.sample_size_f32 = a->sample_size_f32; d.hyper_dev = a->hyper_dev;
+  fill_adam_args(a, d);
   adam_flat_kernel<<<elementwise_grid(n / 4 + 1, 256), 256, 0, (cudaStream_t)stream>>>(p, g, m, v, (__nv_bfloat16*)p_bf16, n, d);
   B200_LAUNCHED("adam_flat_kernel");
   return 0;

@@ -12,9 +12,10 @@
 //      ((W-1) * S inbound, one barrier less);
 //   4. signals completion and waits for the peers' completion, so that when the kernel retires the local arena
 //      holds the fully reduced bucket and no peer is still reading it.
-// No host involvement after set-up; a dead peer turns into a trap after a bounded spin instead of a hang.
+// No host involvement after set-up; a dead peer turns into a recorded error after a bounded wait instead of a hang.
 #include <cuda.h>
 #include "common.h"
+#include "optim_math.cuh"
 #include "../include/b200seq.h"
 
 #include <cstring>
@@ -23,6 +24,7 @@ namespace b200 {
 
 constexpr int kMaxRanks = 8;
 constexpr int kP2PThreads = 512;
+constexpr int kOneShotMaxBlocks = 64;
 
 struct P2PArgs {
   float* data[kMaxRanks];          // peers' arena base pointers (data[rank] is local)
@@ -34,6 +36,7 @@ struct P2PArgs {
   int max_buckets;
   unsigned int* epoch_dev;         // local: per-bucket epoch words (advanced by the kernel itself)
   int one_shot;
+  int scatter_only;                // reduce-scatter mode: keep the sum of my slice locally, send nothing back
   float* sq_out;                   // local, optional: += sum of squares of the reduced values this rank produced
   float* mc;                       // multicast (NVLS) address of the arena, or null
 };
@@ -82,16 +85,31 @@ __device__ __forceinline__ float block_sum(float v) {
   return t;   // valid in thread 0
 }
 
-__device__ __forceinline__ void wait_flag(const unsigned int* p, unsigned int epoch) {
-  long long t0 = clock64();
+// Watchdog.  A rank that never signals (dead process, stalled host) must not hang its peers for ever, and must not
+// take their CUDA contexts down either: after g_wd_cycles SM cycles the waiting thread records
+// (0x80000000 | slot << 8 | missing rank) in a word of mapped host memory (b200_p2p_set_watchdog), raises a
+// device-wide "tripped" flag and gives up the wait.  The kernel then runs to completion on incomplete data, every
+// later wait returns at once, and the host — which looks at the word after each step — stops the run with a
+// message that names the missing rank.  No trap, so the context (and the device) stay usable for an orderly exit.
+__device__ long long g_wd_cycles = 1200000000000ll;   // ~600 s at 1.965 GHz
+__device__ unsigned int* g_wd_err = nullptr;
+__device__ unsigned int g_wd_tripped = 0;
+
+__device__ __forceinline__ bool wait_flag(const unsigned int* p, unsigned int epoch, int slot, int peer) {
+  const long long t0 = clock64();
   // epochs only grow; (int) difference handles wrap-around
   while ((int)(ld_acquire_sys(p) - epoch) < 0) {
-    if (clock64() - t0 > 20000000000ll) {   // ~10 s
-      printf("b200seq p2p: peer flag wait timed out (block %d, want epoch %u, have %u)\n", blockIdx.x, epoch, *p);
-      __trap();
+    const bool tripped = *reinterpret_cast<volatile unsigned int*>(&g_wd_tripped) != 0u;
+    if (tripped || clock64() - t0 > g_wd_cycles) {
+      if (!tripped && atomicExch(&g_wd_tripped, 1u) == 0u && g_wd_err != nullptr) {
+        *reinterpret_cast<volatile unsigned int*>(g_wd_err) = 0x80000000u | ((unsigned)slot << 8) | (unsigned)peer;
+        __threadfence_system();
+      }
+      return false;
     }
     __nanosleep(64);
   }
+  return true;
 }
 
 __device__ __forceinline__ int flag_index(int phase, int bucket, int src, int max_buckets) {
@@ -110,7 +128,7 @@ p2p_allreduce_kernel(const P2PArgs a) {
     __threadfence_system();
     st_release_sys(a.flags[t] + flag_index(0, a.bucket, a.rank, a.max_buckets), epoch);
   }
-  if (t < a.world && t != a.rank) wait_flag(a.flags[a.rank] + flag_index(0, a.bucket, t, a.max_buckets), epoch);
+  if (t < a.world && t != a.rank) wait_flag(a.flags[a.rank] + flag_index(0, a.bucket, t, a.max_buckets), epoch, a.bucket, t);
   __syncthreads();
 
   const long long n4 = a.n >> 2;   // bucket ranges are multiples of 64 elements (arena alignment)
@@ -142,7 +160,7 @@ p2p_allreduce_kernel(const P2PArgs a) {
       if (t == 0) { a.counter[a.bucket] = 0; a.epoch_dev[a.bucket] = epoch; }
       if (t < a.world && t != a.rank) st_release_sys(a.flags[t] + flag_index(1, a.bucket, a.rank, a.max_buckets), epoch);
     }
-    if (t < a.world && t != a.rank) wait_flag(a.flags[a.rank] + flag_index(1, a.bucket, t, a.max_buckets), epoch);
+    if (t < a.world && t != a.rank) wait_flag(a.flags[a.rank] + flag_index(1, a.bucket, t, a.max_buckets), epoch, a.bucket, t);
     __syncthreads();
     if (i < n4) *reinterpret_cast<float4*>(a.data[a.rank] + e) = acc;
     if (a.sq_out != nullptr && (a.bucket % a.world) == a.rank) {       // one rank accounts for a small bucket's norm
@@ -172,7 +190,8 @@ p2p_allreduce_kernel(const P2PArgs a) {
       for (int u = 0; u < U; ++u) {
         const long long i = i0 + u * stride;
         if (i < hi) {
-          multimem_st_f4(a.mc + a.start + (i << 2), v[u]);
+          if (a.scatter_only) *reinterpret_cast<float4*>(a.data[a.rank] + a.start + (i << 2)) = v[u];
+          else multimem_st_f4(a.mc + a.start + (i << 2), v[u]);
           sq += v[u].x * v[u].x + v[u].y * v[u].y + v[u].z * v[u].z + v[u].w * v[u].w;
         }
       }
@@ -181,7 +200,7 @@ p2p_allreduce_kernel(const P2PArgs a) {
     const long long per = ((n4 + a.world - 1) / a.world);
     const long long lo = per * a.rank, hi = (lo + per < n4) ? lo + per : n4;
     const long long stride = (long long)gridDim.x * blockDim.x;
-    constexpr int U = 4;                      // independent 16-byte requests per peer in flight per thread
+    constexpr int U = 2;                      // independent 16-byte requests per peer in flight per thread (U x W float4 live: 4 would spill)
     for (long long i0 = lo + (long long)blockIdx.x * blockDim.x + t; i0 < hi; i0 += U * stride) {
       float4 v[U][kMaxRanks];
 #pragma unroll
@@ -203,9 +222,13 @@ p2p_allreduce_kernel(const P2PArgs a) {
 #pragma unroll
           for (int p = 0; p < kMaxRanks; ++p)      // fixed rank order -> identical bits on every rank
             if (p < a.world) { acc.x += v[u][p].x; acc.y += v[u][p].y; acc.z += v[u][p].z; acc.w += v[u][p].w; }
+          if (a.scatter_only) {
+            *reinterpret_cast<float4*>(a.data[a.rank] + e) = acc;
+          } else {
 #pragma unroll
-          for (int p = 0; p < kMaxRanks; ++p)
-            if (p < a.world) st_peer_f4(a.data[p] + e, acc);
+            for (int p = 0; p < kMaxRanks; ++p)
+              if (p < a.world) st_peer_f4(a.data[p] + e, acc);
+          }
           sq += acc.x * acc.x + acc.y * acc.y + acc.z * acc.z + acc.w * acc.w;
         }
       }
@@ -226,10 +249,124 @@ p2p_allreduce_kernel(const P2PArgs a) {
   __syncthreads();
   if (!last) return;
   if (t == 0) { a.counter[a.bucket] = 0; a.epoch_dev[a.bucket] = epoch; }
+  // reduce-scatter mode has no second round: nothing was written into a peer, and the peers learn that this rank
+  // is done reading THEIR gradients from the next collective it joins (the statistics tail), before any of them
+  // touches its gradient arena again.
+  if (a.scatter_only) return;
   if (t < a.world && t != a.rank) {
     __threadfence_system();
     st_release_sys(a.flags[t] + flag_index(1, a.bucket, a.rank, a.max_buckets), epoch);
-    wait_flag(a.flags[a.rank] + flag_index(1, a.bucket, t, a.max_buckets), epoch);
+    wait_flag(a.flags[a.rank] + flag_index(1, a.bucket, t, a.max_buckets), epoch, a.bucket, t);
+  }
+}
+
+
+// ---- sharded optimizer step: Adam on my slice of every bucket, new parameters written into every rank -------------
+// The gradient of my slice is already the sum over ranks (reduce-scatter kernels above) and the global norm is in
+// device memory (statistics tail), so this is the third and last stage of the fused path
+//   reduce-scatter (per bucket, under backward)  ->  {stats, sum g^2} one-shot  ->  scale / clip / Adam / broadcast.
+// Optimizer work per rank is 1/W of the replicated kernel's; what crosses NVLink is the parameters (once, through
+// multimem.st where the arena has a multicast mapping) instead of the reduced gradients.
+struct ShardedAdamArgs {
+  float* param[kMaxRanks];           // fp32 masters of every rank as mapped here (param[rank] local)
+  float* param_mc;                   // multicast address of the masters, or null
+  __nv_bfloat16* p16[kMaxRanks];     // bf16 working copies (null in fp32/tf32 mode)
+  __nv_bfloat16* p16_mc;
+  float* grad; float* m; float* v;   // local
+  const long long* ranges;           // device: {start, n} per bucket
+  int n_buckets;
+  unsigned int* flags[kMaxRanks];
+  unsigned int* counter;
+  int rank, world, bucket, max_buckets;
+  unsigned int* epoch_dev;
+  AdamArgsDev adam;
+};
+
+__device__ __forceinline__ void multimem_st_bf16x4(__nv_bfloat16* mc, uint32_t lo, uint32_t hi) {
+  asm volatile("multimem.st.relaxed.sys.global.v2.bf16x2 [%0], {%1, %2};" ::"l"(mc), "r"(lo), "r"(hi) : "memory");
+}
+
+__global__ void __launch_bounds__(256)
+p2p_sharded_adam_kernel(const ShardedAdamArgs a) {
+  const int t = threadIdx.x;
+  const unsigned int epoch = a.epoch_dev[a.bucket] + 1u;
+  AdamArgsDev ad = a.adam;
+  float decay = 1.f - ad.weight_decay * ad.lr;
+  if (ad.hyper_dev != nullptr) {
+    ad.lr = ad.hyper_dev[0];
+    ad.step_size = ad.hyper_dev[1];
+    decay = ad.hyper_dev[2];
+  }
+  const StepScalars sc = derive_scalars(ad.mult, ad.sample_size, ad.sample_size_f32, ad.norm_sq, ad.max_norm);
+  if (blockIdx.x == 0 && t == 0 && ad.stats_out != nullptr) {
+    ad.stats_out[0] = sc.gnorm;
+    ad.stats_out[1] = sc.scale;
+    ad.stats_out[2] = sc.clipped;
+  }
+  const float one_m_b1 = 1.f - ad.beta1, one_m_b2 = 1.f - ad.beta2;
+  const bool decay_on = ad.weight_decay != 0.f;
+  const long long gtid = (long long)blockIdx.x * blockDim.x + t;
+  const long long gstride = (long long)gridDim.x * blockDim.x;
+  const bool bf16_mode = a.p16[a.rank] != nullptr;
+  float* const p_local = a.param[a.rank];
+
+  for (int b = 0; b < a.n_buckets; ++b) {
+    const long long start = a.ranges[2 * b], n4 = a.ranges[2 * b + 1] >> 2;
+    const long long per = (n4 + a.world - 1) / a.world;
+    const long long lo = per * a.rank, hi = (lo + per < n4) ? lo + per : n4;
+    for (long long i = lo + gtid; i < hi; i += gstride) {
+      const long long e = start + (i << 2);
+      float4 pv = *reinterpret_cast<const float4*>(p_local + e);
+      const float4 gv = *reinterpret_cast<const float4*>(a.grad + e);
+      float4 mv = *reinterpret_cast<const float4*>(a.m + e);
+      float4 vv = *reinterpret_cast<const float4*>(a.v + e);
+      adam_element(pv.x, gv.x, mv.x, vv.x, sc.scale, ad.beta1, ad.beta2, one_m_b1, one_m_b2, ad.eps, ad.step_size, decay_on, decay);
+      adam_element(pv.y, gv.y, mv.y, vv.y, sc.scale, ad.beta1, ad.beta2, one_m_b1, one_m_b2, ad.eps, ad.step_size, decay_on, decay);
+      adam_element(pv.z, gv.z, mv.z, vv.z, sc.scale, ad.beta1, ad.beta2, one_m_b1, one_m_b2, ad.eps, ad.step_size, decay_on, decay);
+      adam_element(pv.w, gv.w, mv.w, vv.w, sc.scale, ad.beta1, ad.beta2, one_m_b1, one_m_b2, ad.eps, ad.step_size, decay_on, decay);
+      *reinterpret_cast<float4*>(a.m + e) = mv;
+      *reinterpret_cast<float4*>(a.v + e) = vv;
+      *reinterpret_cast<float4*>(a.grad + e) = make_float4(0.f, 0.f, 0.f, 0.f);
+      if (bf16_mode) {
+        // the fp32 master of a slice lives with its owner only; the bf16 working copy is what every rank computes with
+        *reinterpret_cast<float4*>(p_local + e) = pv;
+        __nv_bfloat162 q0 = __floats2bfloat162_rn(pv.x, pv.y), q1 = __floats2bfloat162_rn(pv.z, pv.w);
+        const uint32_t w0 = *reinterpret_cast<uint32_t*>(&q0), w1 = *reinterpret_cast<uint32_t*>(&q1);
+        if (a.p16_mc != nullptr) {
+          multimem_st_bf16x4(a.p16_mc + e, w0, w1);
+        } else {
+#pragma unroll
+          for (int p = 0; p < kMaxRanks; ++p)
+            if (p < a.world) *reinterpret_cast<uint2*>(a.p16[p] + e) = make_uint2(w0, w1);
+        }
+      } else if (a.param_mc != nullptr) {
+        multimem_st_f4(a.param_mc + e, pv);
+      } else {
+#pragma unroll
+        for (int p = 0; p < kMaxRanks; ++p)
+          if (p < a.world) st_peer_f4(a.param[p] + e, pv);
+      }
+    }
+    // gradients outside my slice were only inputs to the peers' reductions: clear them for the next backward
+    for (long long i = gtid; i < n4; i += gstride)
+      if (i < lo || i >= hi) *reinterpret_cast<float4*>(a.grad + start + (i << 2)) = make_float4(0.f, 0.f, 0.f, 0.f);
+  }
+
+  // ---- completion round: when this kernel retires, every peer's slice has landed in this rank's parameters ----
+  __shared__ bool last;
+  __threadfence_system();
+  __syncthreads();
+  if (t == 0) {
+    const unsigned int prev = atomicAdd(a.counter + a.bucket, 1u);
+    last = (prev == gridDim.x - 1);
+  }
+  __syncthreads();
+  if (!last) return;
+  if (t == 0) { a.counter[a.bucket] = 0; a.epoch_dev[a.bucket] = epoch; }
+  if (t < a.world && t != a.rank) {
+    __threadfence_system();
+    st_release_sys(a.flags[t] + flag_index(1, a.bucket, a.rank, a.max_buckets), epoch);
+    wait_flag(a.flags[a.rank] + flag_index(1, a.bucket, t, a.max_buckets), epoch, a.bucket, t);
   }
 }
 
@@ -280,13 +417,13 @@ extern "C" int b200_ipc_close(void* base) {
   return 0;
 }
 
-extern "C" int b200_p2p_allreduce(void* const* data_ptrs, void* const* flag_ptrs, void* counter, int rank, int world,
-                                  long long start, long long n, int bucket, int max_buckets, void* epoch_dev,
-                                  int one_shot, int blocks, float* sq_out, void* multicast_base, void* stream) {
-  if (!data_ptrs || !flag_ptrs || !counter || !epoch_dev) return fail(B200_ERR_ARG, "p2p_allreduce: null pointer");
-  if (world < 2 || world > kMaxRanks || rank < 0 || rank >= world) return fail(B200_ERR_ARG, "p2p_allreduce: bad rank/world %d/%d", rank, world);
-  if ((start & 3) || (n & 3)) return fail(B200_ERR_ARG, "p2p_allreduce: range must be a multiple of 4 elements");
-  if (bucket < 0 || bucket >= max_buckets) return fail(B200_ERR_ARG, "p2p_allreduce: bucket index out of range");
+static int launch_reduce(void* const* data_ptrs, void* const* flag_ptrs, void* counter, int rank, int world,
+                         long long start, long long n, int bucket, int max_buckets, void* epoch_dev, int one_shot,
+                         int scatter_only, int blocks, float* sq_out, void* multicast_base, void* stream, const char* who) {
+  if (!data_ptrs || !flag_ptrs || !counter || !epoch_dev) return fail(B200_ERR_ARG, "%s: null pointer", who);
+  if (world < 2 || world > kMaxRanks || rank < 0 || rank >= world) return fail(B200_ERR_ARG, "%s: bad rank/world %d/%d", who, rank, world);
+  if ((start & 3) || (n & 3)) return fail(B200_ERR_ARG, "%s: range must be a multiple of 4 elements", who);
+  if (bucket < 0 || bucket >= max_buckets) return fail(B200_ERR_ARG, "%s: bucket index out of range", who);
   P2PArgs a;
   for (int i = 0; i < kMaxRanks; ++i) {
     a.data[i] = i < world ? static_cast<float*>(data_ptrs[i]) : nullptr;
@@ -294,7 +431,7 @@ extern "C" int b200_p2p_allreduce(void* const* data_ptrs, void* const* flag_ptrs
   }
   a.counter = static_cast<unsigned int*>(counter);
   a.rank = rank; a.world = world; a.start = start; a.n = n; a.bucket = bucket; a.max_buckets = max_buckets;
-  a.epoch_dev = static_cast<unsigned int*>(epoch_dev); a.one_shot = one_shot;
+  a.epoch_dev = static_cast<unsigned int*>(epoch_dev); a.one_shot = one_shot; a.scatter_only = scatter_only;
   a.sq_out = sq_out;
   a.mc = one_shot ? nullptr : static_cast<float*>(multicast_base);
   if (blocks <= 0) blocks = 32;
@@ -305,15 +442,84 @@ extern "C" int b200_p2p_allreduce(void* const* data_ptrs, void* const* flag_ptrs
   if (blocks >= 1000) {
     threads = blocks / 1000;
     blocks %= 1000;
-    if (threads < 32 || threads > kP2PThreads || (threads & 31) || blocks < 1) return fail(B200_ERR_ARG, "p2p_allreduce: bad threads/blocks encoding");
+    if (threads < 32 || threads > kP2PThreads || (threads & 31) || blocks < 1) return fail(B200_ERR_ARG, "%s: bad threads/blocks encoding", who);
   }
   if (one_shot) {
+    // Every block of a one-shot launch spins on a flag that a peer raises only after ALL of its blocks have
+    // arrived, so the whole grid has to be resident at once — also next to a persistent GEMM that leaves room for
+    // at most a few extra 512-thread CTAs per SM.  64 blocks (128 KB per rank) stay far below that.
     threads = kP2PThreads;
     const long long need = ((n >> 2) + kP2PThreads - 1) / kP2PThreads;
-    if (need > 4 * num_sms()) return fail(B200_ERR_ARG, "p2p_allreduce: bucket too large for one-shot mode");
+    if (need > kOneShotMaxBlocks) return fail(B200_ERR_ARG, "%s: bucket too large for one-shot mode (%lld blocks > %d)", who, need, kOneShotMaxBlocks);
     blocks = (int)(need > 0 ? need : 1);
   }
   p2p_allreduce_kernel<<<blocks, threads, 0, (cudaStream_t)stream>>>(a);
   B200_LAUNCHED("p2p_allreduce_kernel");
+  return 0;
+}
+
+extern "C" int b200_p2p_allreduce(void* const* data_ptrs, void* const* flag_ptrs, void* counter, int rank, int world,
+                                  long long start, long long n, int bucket, int max_buckets, void* epoch_dev,
+                                  int one_shot, int blocks, float* sq_out, void* multicast_base, void* stream) {
+  return launch_reduce(data_ptrs, flag_ptrs, counter, rank, world, start, n, bucket, max_buckets, epoch_dev, one_shot, 0,
+                       blocks, sq_out, multicast_base, stream, "p2p_allreduce");
+}
+
+extern "C" int b200_p2p_reduce_scatter(void* const* data_ptrs, void* const* flag_ptrs, void* counter, int rank, int world,
+                                       long long start, long long n, int bucket, int max_buckets, void* epoch_dev,
+                                       int blocks, float* sq_out, void* multicast_base, void* stream) {
+  return launch_reduce(data_ptrs, flag_ptrs, counter, rank, world, start, n, bucket, max_buckets, epoch_dev, 0, 1,
+                       blocks, sq_out, multicast_base, stream, "p2p_reduce_scatter");
+}
+
+extern "C" int b200_p2p_sharded_adam(void* const* param_ptrs, void* param_mc, void* const* bf16_ptrs, void* bf16_mc,
+                                     float* grad, float* m, float* v, const long long* ranges, int n_buckets, long long total,
+                                     void* const* flag_ptrs, void* counter, int rank, int world, int bucket, int max_buckets,
+                                     void* epoch_dev, const b200_adam_args* args, int blocks, void* stream) {
+  if (!param_ptrs || !grad || !m || !v || !ranges || !flag_ptrs || !counter || !epoch_dev || !args)
+    return fail(B200_ERR_ARG, "p2p_sharded_adam: null pointer");
+  if (world < 2 || world > kMaxRanks || rank < 0 || rank >= world) return fail(B200_ERR_ARG, "p2p_sharded_adam: bad rank/world %d/%d", rank, world);
+  if (bucket < 0 || bucket >= max_buckets || n_buckets < 1) return fail(B200_ERR_ARG, "p2p_sharded_adam: bad bucket arguments");
+  if (total & 3) return fail(B200_ERR_ARG, "p2p_sharded_adam: arena size must be a multiple of 4 elements");
+  ShardedAdamArgs a;
+  for (int i = 0; i < kMaxRanks; ++i) {
+    a.param[i] = i < world ? static_cast<float*>(param_ptrs[i]) : nullptr;
+    a.p16[i] = (bf16_ptrs && i < world) ? static_cast<__nv_bfloat16*>(bf16_ptrs[i]) : nullptr;
+    a.flags[i] = i < world ? static_cast<unsigned int*>(flag_ptrs[i]) : nullptr;
+  }
+  if (!a.param[rank]) return fail(B200_ERR_ARG, "p2p_sharded_adam: local parameter pointer missing");
+  if (((reinterpret_cast<uintptr_t>(a.param[rank]) | reinterpret_cast<uintptr_t>(grad) | reinterpret_cast<uintptr_t>(m) |
+        reinterpret_cast<uintptr_t>(v)) & 15) != 0)
+    return fail(B200_ERR_ARG, "p2p_sharded_adam: buffers must be 16-byte aligned");
+  a.param_mc = static_cast<float*>(param_mc);
+  a.p16_mc = bf16_ptrs ? static_cast<__nv_bfloat16*>(bf16_mc) : nullptr;
+  a.grad = grad; a.m = m; a.v = v; a.ranges = ranges; a.n_buckets = n_buckets;
+  a.counter = static_cast<unsigned int*>(counter);
+  a.rank = rank; a.world = world; a.bucket = bucket; a.max_buckets = max_buckets;
+  a.epoch_dev = static_cast<unsigned int*>(epoch_dev);
+  fill_adam_args(args, a.adam);
+  if (blocks <= 0) blocks = num_sms() * 8;
+  p2p_sharded_adam_kernel<<<blocks, 256, 0, (cudaStream_t)stream>>>(a);
+  B200_LAUNCHED("p2p_sharded_adam_kernel");
+  return 0;
+}
+
+extern "C" int b200_p2p_set_watchdog(double timeout_seconds, unsigned int* host_error_word_devptr) {
+  if (!(timeout_seconds > 0)) return fail(B200_ERR_ARG, "p2p_set_watchdog: timeout must be positive");
+  int dev = 0, khz = 0;
+  B200_CUDA(cudaGetDevice(&dev));
+  cudaDeviceGetAttribute(&khz, cudaDevAttrClockRate, dev);
+  if (khz <= 0) khz = 1965000;
+  double cyc = timeout_seconds * 1e3 * (double)khz;
+  if (cyc > 9e18) cyc = 9e18;
+  const long long cycles = (long long)cyc;
+  B200_CUDA(cudaMemcpyToSymbol(g_wd_cycles, &cycles, sizeof(cycles)));
+  B200_CUDA(cudaMemcpyToSymbol(g_wd_err, &host_error_word_devptr, sizeof(host_error_word_devptr)));
+  return 0;
+}
+
+extern "C" int b200_p2p_watchdog_reset(void) {
+  const unsigned int zero = 0;
+  B200_CUDA(cudaMemcpyToSymbol(g_wd_tripped, &zero, sizeof(zero)));
   return 0;
 }

@@ -121,6 +121,8 @@ def save_checkpoint(args, controller, epoch_itr, val_loss):
     if getattr(args, "no_save", False):
         return
     master = distributed_utils.is_master(args)
+    if hasattr(controller, "prepare_checkpoint"):
+        controller.prepare_checkpoint()       # every rank: sharded optimizer state is gathered before the master writes
     prev_best = getattr(save_checkpoint, "best", val_loss)
     if val_loss is not None:
         better = max if getattr(args, "maximize_best_checkpoint_metric", False) else min

@@ -104,7 +104,6 @@ class Controller:
         self._graph_enabled = bool(getattr(args, "cuda_graph", False)) and self.cuda
         self._graph = None
         self._g_raw = None
-        self._graph_sig = None
         self._graph_cache: Dict[Any, Dict[str, Any]] = {}     # batch signature -> captured step
         self._graph_seen_by_sig: Dict[Any, int] = {}
         self._graph_steps_total = 0
@@ -134,17 +133,31 @@ class Controller:
         params = [p for p in model.parameters() if p.requires_grad]
         groups = model.arena_groups() if hasattr(model, "arena_groups") else None
         bucket_mb = int(getattr(self.args, "bucket_cap_mb", 25))
-        grad_alloc = None
+        alloc = None
+        want_sharded = False
         if self.cuda and self.world_size > 1 and getattr(self.args, "comm", "auto") in ("auto", "p2p"):
-            from .parallel.p2p import symmetric_grad_alloc
-            grad_alloc = symmetric_grad_alloc          # NVLS-capable memory when the platform offers it
+            from .parallel import p2p
+            # sharded optimizer step (reduce-scatter -> Adam on the owned slice -> parameter broadcast) needs the
+            # parameters, not only the gradients, in memory that every rank has mapped
+            want_sharded = (getattr(self.args, "optimizer", "adam") == "adam"
+                            and not getattr(self.args, "no_sharded_optimizer", False)
+                            and not os.environ.get("B200_NO_SHARDED")
+                            and p2p.CommRuntime.get() is not None)
+            bf16 = compute_dtype == torch.bfloat16
+
+            def alloc(kind, numel, dtype):
+                if kind == "grad":
+                    return p2p.symmetric_grad_alloc(numel)     # NVLS-capable memory when the platform offers it
+                if want_sharded and kind == ("work" if bf16 else "master"):
+                    return p2p.symmetric_alloc(numel, dtype)
+                return None
             # every bucket of the peer-to-peer reducer costs two flag rounds across all ranks plus a launch; measured on
             # 2 B200 (ms/step): 25 MB 8.52, 50 MB 8.43, 100 MB 8.35, 250 MB 8.47, 500 MB 8.73 (profiles/README.md §1)
             bucket_mb = int(getattr(self.args, "p2p_bucket_mb", 100) or bucket_mb)
-        bucket_bytes = int(os.environ.get("B200_BUCKET_MB") or bucket_mb) * 1024 * 1024
+        bucket_bytes = int(os.environ.get("B200_BUCKET_BYTES") or int(os.environ.get("B200_BUCKET_MB") or bucket_mb) * 1024 * 1024)
         self._arena = ParamArena(params, groups=groups, device=self.device, compute_dtype=compute_dtype,
-                                 bucket_bytes=bucket_bytes, grad_alloc=grad_alloc)
-        self._reducer = build_reducer(self.args, self._arena, self.world_size)
+                                 bucket_bytes=bucket_bytes, alloc=alloc)
+        self._reducer = build_reducer(self.args, self._arena, self.world_size, sharded=want_sharded)
         use_native = self.cuda and not getattr(self.args, "no_native", False) and self.precision != "fp32"
         if hasattr(model, "bind_arena"):
             model.bind_arena(self._arena if use_native else None, self._reducer)
@@ -204,8 +217,20 @@ class Controller:
     def _meters_state(self):
         return {k: {"type": type(v).__name__, "state": v.state_dict()} for k, v in self.meters.items()}
 
+    def prepare_checkpoint(self):
+        """Collective (every rank): with the sharded optimizer step each rank keeps only its slices of the Adam
+        moments (and, in bf16 mode, of the fp32 masters) current — gather them so that the master rank can write the
+        reference's checkpoint schema unchanged."""
+        self.flush_stats()
+        red = self._reducer
+        if red is not None and getattr(red, "sharded", False) and self._optimizer is not None:
+            flats = list(self._optimizer.optimizer.flat_state_tensors())
+            if self._arena.work is not None:
+                flats.append(self._arena.master)
+            red.gather_sharded(flats)
+
     def save_checkpoint(self, filename, extra_state):
-        """Write all training state (master rank only)."""
+        """Write all training state (master rank only; ``prepare_checkpoint`` must have run on every rank)."""
         self.flush_stats()
         if distributed_utils.is_master(self.args):
             extra_state = dict(extra_state)
@@ -330,21 +355,31 @@ class Controller:
 
     # ---- the hot loop -----------------------------------------------------------------------------------
     def train_step(self, samples, dummy_batch=False, raise_oom=False):
-        """Forward, backward, cross-rank reduction and parameter update for one group of micro-batches."""
+        """Forward, backward, cross-rank reduction and parameter update for one group of micro-batches.
+
+        Eager launches and CUDA-graph replays issue the SAME sequence of cross-rank operations (one reduction per
+        bucket, one reduction of the statistics tail, the parameter broadcast of the sharded update), so ranks may
+        take different paths in the same step — a rank with the end-of-epoch filler batch or a new batch shape runs
+        eagerly (or captures) while its peers replay."""
         if self._dummy_batch is None:
             self._dummy_batch = samples[0]
         model, optimizer, reducer = self.model, self.optimizer, self.reducer
         self._settle_gc()
         if self._graph_enabled and not dummy_batch and self._graphable(samples):
-            return self._graph_train_step(samples[0])
+            return self._graph_train_step(samples)
         self._set_seed()
         model.train()
         if not dummy_batch:
             self.meters["train_wall"].start()
+        if self.cuda:
+            return self._eager_step_cuda(samples, dummy_batch)
+        return self._eager_step_cpu(samples, dummy_batch)
 
-        dev = self.device
-        stat_sum = torch.zeros(self._mailbox.FIELDS, dtype=torch.float64, device=dev)
-        host_stats = [0.0] * 5            # sample_size, nsentences, ntokens, (last) sample_size, n_real
+    def _run_micro_batches(self, samples, on_loss):
+        """Forward + backward of every micro-batch; reductions start under the last one.  Returns host-side sums
+        [sample_size, nsentences, ntokens] and the last real micro-batch's (logging_output, sample_size)."""
+        reducer = self._reducer
+        host_stats = [0.0, 0.0, 0.0]
         last_logging, last_sample_size = None, 0
         for i, sample in enumerate(samples):
             sample = self._prepare_sample(sample)
@@ -355,7 +390,7 @@ class Controller:
             reducer.begin(sync_now=(i == len(samples) - 1))
             try:
                 with self._range("forward_backward"):
-                    loss, sample_size, logging_output = self.task.train_step(sample, model, optimizer, ignore_grad)
+                    loss, sample_size, logging_output = self.task.train_step(sample, self._model, self._optimizer, ignore_grad)
             except RuntimeError as e:
                 if "out of memory" in str(e):
                     raise RuntimeError("ran out of memory with exception: {}".format(e))
@@ -364,22 +399,102 @@ class Controller:
                 host_stats[0] += sample_size
                 host_stats[1] += logging_output.get("nsentences", 0)
                 host_stats[2] += logging_output.get("ntokens", 0)
-                stat_sum[0] += _as_dev_scalar(logging_output.get("loss", 0.0), dev)
-                stat_sum[1] += _as_dev_scalar(logging_output.get("nll_loss", 0.0), dev)
+                on_loss(logging_output)
                 last_logging, last_sample_size = logging_output, sample_size
+        return host_stats, last_logging, last_sample_size
+
+    def _device_update(self, tail, sample_size_dev, mult, hyper_dev=None, advance=True):
+        """After backward: wait for the bucket reductions, reduce the statistics tail, then scale / clip / update in
+        one kernel (on the slices this rank owns when the reducer is sharded).  Runs eagerly or under graph capture."""
+        from .ops import kernels
+        arena, reducer, opt = self._arena, self._reducer, self._optimizer.optimizer
+        ws = kernels.Workspace.get(self.device)
+        with self._range("reduce_wait"):
+            reducer.finish()
+            if self.world_size > 1:
+                reducer.reduce_tail()
+        if self.world_size > 1 and getattr(reducer, "fused_norm", False):
+            from .parallel.p2p import SQ_SLOT
+            norm_sq = tail[SQ_SLOT:SQ_SLOT + 1]       # summed over ranks by reduce_tail: no separate norm pass
+        else:
+            kernels.sumsq(arena.grad, ws.norm_sq, ws=ws)
+            norm_sq = ws.norm_sq
+        kw = dict(grad_scale_mult=mult, max_norm=float(getattr(self.args, "clip_norm", 0.0)), norm_sq=norm_sq,
+                  sample_size=sample_size_dev, stats_out=ws.step_stats, hyper_dev=hyper_dev, advance=advance)
+        with self._range("update"):
+            if getattr(reducer, "sharded", False):
+                opt.sharded_step(reducer, **kw)
+            else:
+                opt.fused_step(zero_grad=True, **kw)
+        return ws.step_stats
+
+    def _eager_step_cuda(self, samples, dummy_batch):
+        dev = self.device
+        tail = self._arena.tail
+        tail.zero_()
+        stat_sum = torch.zeros(self._mailbox.FIELDS, dtype=torch.float64, device=dev)
+
+        def on_loss(lo):
+            stat_sum[0] += _as_dev_scalar(lo.get("loss", 0.0), dev)
+            stat_sum[1] += _as_dev_scalar(lo.get("nll_loss", 0.0), dev)
+        host_stats, last_logging, last_sample_size = self._run_micro_batches(samples, on_loss)
+        if dummy_batch:
+            with self._range("reduce_wait"):
+                self._reducer.finish()
+            return None
+
+        # ---- statistics: global sums ride the tail (one peer reduction, no NCCL call, no host sync) --------------
+        if self.fast_stat_sync:
+            if getattr(self, "_stat_stage", None) is None:
+                self._stat_stage = [torch.zeros(3, dtype=torch.float32).pin_memory() for _ in range(4)]
+                self._stat_stage_i = 0
+            st = self._stat_stage[self._stat_stage_i % 4]
+            self._stat_stage_i += 1
+            st[0], st[1], st[2] = host_stats[0], host_stats[1], host_stats[2]
+            tail[0:2] = stat_sum[0:2].float()
+            tail[2:5].copy_(st, non_blocking=True)
+            sample_size_dev, mult = tail[2:3], 1.0
+        else:
+            if self.world_size > 1 and not self._graph_enabled:
+                # reference's slow path (hetseq/controller.py:316-329): host statistics + previous grad norm of every
+                # rank; with --cuda-graph the replicas' identity is guaranteed by construction and the check is skipped
+                gathered = distributed_utils.all_gather_list([host_stats[:3], self._prev_grad_norm_host()])
+                norms = [g[1] for g in gathered]
+                if not getattr(self.args, "use_bmuf", False):
+                    assert all(n == norms[0] for n in norms) or all(n is None or math.isnan(n) or math.isinf(n) for n in norms), \
+                        "Fatal error: gradients are inconsistent between workers"
+            sample_size_dev = None
+            mult = 1.0 / float(last_sample_size) if last_sample_size and last_sample_size > 0 else 1.0
+        step_stats = self._device_update(tail, sample_size_dev, mult)
+        if self.fast_stat_sync:
+            stat_sum[0:5] = tail[0:5].double()
+        else:
+            ll = last_logging or {}
+            stat_sum[0] = _as_dev_scalar(ll.get("loss", 0.0), dev)
+            stat_sum[1] = _as_dev_scalar(ll.get("nll_loss", 0.0), dev)
+            stat_sum[2:5] = torch.tensor([float(last_sample_size), float(ll.get("nsentences", 0)), float(ll.get("ntokens", 0))],
+                                         dtype=torch.float64).to(dev, non_blocking=True)
+        stat_sum[5:7] = step_stats[0:3:2].double()
+        return self._finish_step(stat_sum)
+
+    def _eager_step_cpu(self, samples, dummy_batch):
+        dev = self.device
+        optimizer, reducer = self._optimizer, self._reducer
+        stat_sum = torch.zeros(self._mailbox.FIELDS, dtype=torch.float64, device=dev)
+
+        def on_loss(lo):
+            stat_sum[0] += _as_dev_scalar(lo.get("loss", 0.0), dev)
+            stat_sum[1] += _as_dev_scalar(lo.get("nll_loss", 0.0), dev)
+        host_stats, last_logging, last_sample_size = self._run_micro_batches(samples, on_loss)
         with self._range("reduce_wait"):
             reducer.finish()
         if dummy_batch:
             return None
-
-        # ---- statistics -----------------------------------------------------------------------------------
-        sample_size_dev = None
         if self.fast_stat_sync:
-            stat_sum[2:5] += torch.tensor(host_stats[:3], dtype=torch.float64).to(dev, non_blocking=True)
+            stat_sum[2:5] += torch.tensor(host_stats[:3], dtype=torch.float64)
             if self.world_size > 1:
                 torch.distributed.all_reduce(stat_sum[:5])
-            sample_size_dev = stat_sum[2:3]
-            sample_size = None                     # lives on the device
+            ss = float(stat_sum[2].item())
         else:
             if self.world_size > 1:
                 gathered = distributed_utils.all_gather_list([host_stats[:3], self._prev_grad_norm_host()])
@@ -387,46 +502,27 @@ class Controller:
                 if not getattr(self.args, "use_bmuf", False):
                     assert all(n == norms[0] for n in norms) or all(n is None or math.isnan(n) or math.isinf(n) for n in norms), \
                         "Fatal error: gradients are inconsistent between workers"
-            sample_size = last_sample_size
-            stat_sum[2:5] = torch.tensor([float(last_sample_size), float((last_logging or {}).get("nsentences", 0)),
-                                          float((last_logging or {}).get("ntokens", 0))], dtype=torch.float64).to(dev, non_blocking=True)
+            ss = float(last_sample_size)
+            ll = last_logging or {}
+            stat_sum[2:5] = torch.tensor([ss, float(ll.get("nsentences", 0)), float(ll.get("ntokens", 0))], dtype=torch.float64)
             if last_logging is not None:
-                stat_sum[0] = _as_dev_scalar(last_logging.get("loss", 0.0), dev)
-                stat_sum[1] = _as_dev_scalar(last_logging.get("nll_loss", 0.0), dev)
-
-        # ---- scale, clip, update: one fused kernel on the arena -------------------------------------------
+                stat_sum[0] = _as_dev_scalar(ll.get("loss", 0.0), dev)
+                stat_sum[1] = _as_dev_scalar(ll.get("nll_loss", 0.0), dev)
         clip_norm = float(getattr(self.args, "clip_norm", 0.0))
-        if self.cuda:
-            from .ops import kernels
-            if getattr(self, "_nvtx", False):
-                torch.cuda.nvtx.range_push("update")
-            ws = kernels.Workspace.get(dev)
-            kernels.sumsq(self._arena.grad, ws.norm_sq, ws=ws)
-            if sample_size_dev is not None:
-                mult, ss_dev = 1.0, sample_size_dev
-            else:
-                mult, ss_dev = (1.0 / float(sample_size) if sample_size and sample_size > 0 else 1.0), None
-            optimizer.optimizer.fused_step(grad_scale_mult=mult, max_norm=clip_norm, norm_sq=ws.norm_sq,
-                                           sample_size=ss_dev, stats_out=ws.step_stats, zero_grad=True)
-            stat_sum[5:7] = ws.step_stats[0:3:2].double()
-            if getattr(self, "_nvtx", False):
-                torch.cuda.nvtx.range_pop()
-        else:
-            if sample_size_dev is not None:
-                ss = float(sample_size_dev.item())
-            else:
-                ss = float(sample_size)
-            if ss > 0:
-                optimizer.multiply_grads(1.0 / ss)
-            gnorm = optimizer.clip_grad_norm(clip_norm)
-            optimizer.step()
-            optimizer.zero_grad()
-            stat_sum[5] = float(gnorm)
-            stat_sum[6] = 1.0 if (clip_norm > 0 and float(gnorm) > clip_norm) else 0.0
+        if ss > 0:
+            optimizer.multiply_grads(1.0 / ss)
+        gnorm = optimizer.clip_grad_norm(clip_norm)
+        optimizer.step()
+        optimizer.zero_grad()
+        stat_sum[5] = float(gnorm)
+        stat_sum[6] = 1.0 if (clip_norm > 0 and float(gnorm) > clip_norm) else 0.0
+        return self._finish_step(stat_sum)
 
+    def _finish_step(self, stat_sum):
+        if hasattr(self._reducer, "check_watchdog"):
+            self._reducer.check_watchdog()          # a peer never arrived: stop here, with its rank in the message
         self.set_num_updates(self.get_num_updates() + 1)
         self.task.update_step(self._num_updates)
-
         # ---- meters (asynchronously on CUDA) --------------------------------------------------------------
         self._mailbox.post(stat_sum)
         self._consume_stats(keep_latest=1 if self._lazy_stats else 0)
@@ -434,27 +530,29 @@ class Controller:
         return self._last_logging_output if self._last_logging_output is not None else {
             "loss": 0.0, "nll_loss": 0.0, "ntokens": 0, "nsentences": 0, "sample_size": 0}
 
-
     # ---- CUDA-graph path ------------------------------------------------------------------------------------
     # The fixed-shape step (forward, backward, bucket reductions, norm, fused update, statistics) is captured once
     # and replayed; everything that changes from step to step lives in device memory that is refreshed before
-    # the replay with asynchronous copies from pinned buffers: the batch, the dropout seed, and {lr, bias-corrected
-    # step size, decay factor}.  Launch overhead per step drops from ~400 Python->ctypes->CUDA launches to one.
+    # the replay with asynchronous copies from pinned buffers: the batches, the dropout seed, and {lr, bias-corrected
+    # step size, decay factor}.  Launch overhead per step drops from ~400 Python->ctypes->CUDA launches per
+    # micro-batch to one.  A step of several micro-batches (--update-freq) is ONE graph: gradients accumulate in the
+    # arena and the reductions start under the last micro-batch's backward.
     @staticmethod
-    def _sig(sample):
+    def _sig1(sample):
         ts = sample if isinstance(sample, (list, tuple)) else list(sample.values())
         return tuple((tuple(t.shape), str(t.dtype)) for t in ts if torch.is_tensor(t))
 
+    def _sig(self, samples):
+        return tuple(self._sig1(s) for s in samples)
+
     def _graphable(self, samples) -> bool:
-        if len(samples) != 1 or utils.sample_is_empty(samples[0]):
+        if len(samples) < 1 or len(samples) > self.MAX_GRAPH_MICRO or any(utils.sample_is_empty(x) for x in samples):
             return False
-        if self.world_size > 1 and not self.fast_stat_sync:
+        if not all(isinstance(x, (list, tuple, dict)) for x in samples):
             return False
-        if type(self._reducer).__name__ == "TorchReducer":
+        if not hasattr(self.task, "_sample_size"):
             return False
-        if not isinstance(samples[0], (list, tuple, dict)):
-            return False
-        sig = self._sig(samples[0])
+        sig = self._sig(samples)
         if sig in self._graph_cache:
             return True
         # a few eager steps first (lazy initialisation, warm caches); later shapes are captured on their second visit.
@@ -467,78 +565,87 @@ class Controller:
         return self._graph_steps_total > 3 and (seen > 1 or not self._graph_cache)
 
     MAX_GRAPHS = 24
+    MAX_GRAPH_MICRO = 16
 
-    def _graph_body(self):
+    def _graph_body(self, st):
         """One full step on the static buffers (runs eagerly while capturing)."""
         from .ops import kernels
-        arena, reducer, opt = self._arena, self._reducer, self.optimizer.optimizer
-        ws = kernels.Workspace.get(self.device)
+        arena, reducer = self._arena, self._reducer
         tail = arena.tail
         tail.zero_()
-        if self._g_raw is not None:          # packed batch: the assembly kernel is the first node of the graph
-            kernels.assemble_bert_batch(self._g_raw, *self._g_raw_dims, out=self._g_sample)
-        reducer.begin(sync_now=True)
-        loss, sample_size, logging_output = self.task.train_step(self._g_sample, self._model, self.optimizer, False)
-        tail[0:1] += loss.detach().reshape(1).float()
-        tail[1:2] += loss.detach().reshape(1).float()
-        tail[2:5] += self._g_const
-        reducer.finish()
-        if self.world_size > 1:
-            reducer.reduce_tail()
-        if getattr(reducer, "fused_norm", False):
-            from .parallel.p2p import SQ_SLOT
-            norm_sq = tail[SQ_SLOT:SQ_SLOT + 1]       # summed over ranks by reduce_tail: no separate norm pass
+        n = len(st["samples"])
+        for i in range(n):
+            if st["raw"][i] is not None:      # packed batch: the assembly kernel is the first node of the micro-batch
+                kernels.assemble_bert_batch(st["raw"][i], *st["raw_dims"][i], out=st["samples"][i])
+            reducer.begin(sync_now=(i == n - 1))
+            loss, sample_size, logging_output = self.task.train_step(st["samples"][i], self._model, self.optimizer, False)
+            lf = loss.detach().reshape(1).float()
+            tail[0:1] += lf
+            tail[1:2] += lf
+            if i == n - 1:
+                st["last_loss"].copy_(lf)
+        tail[2:5] += st["const"]
+        if self.fast_stat_sync:
+            sample_size_dev = tail[2:3]                       # global sum after reduce_tail
         else:
-            kernels.sumsq(arena.grad, ws.norm_sq, ws=ws)
-            norm_sq = ws.norm_sq
-        opt.fused_step(grad_scale_mult=1.0, max_norm=float(getattr(self.args, "clip_norm", 0.0)), norm_sq=norm_sq,
-                       sample_size=tail[2:3], stats_out=ws.step_stats, zero_grad=True, hyper_dev=self._g_hyper, advance=False)
-        self._g_out[0:5] = tail[0:5].double()
-        self._g_out[5:7] = ws.step_stats[0:3:2].double()
-        return sample_size, logging_output
+            sample_size_dev = st["const_last"][0:1]           # the reference scales by the last local micro-batch's size
+        step_stats = self._device_update(tail, sample_size_dev, 1.0, hyper_dev=self._g_hyper, advance=False)
+        if self.fast_stat_sync:
+            self._g_out[0:5] = tail[0:5].double()
+        else:
+            self._g_out[0:2] = st["last_loss"].double().expand(2)
+            self._g_out[2:5] = st["const_last"].double()
+        self._g_out[5:7] = step_stats[0:3:2].double()
 
-    def _graph_capture(self, sample):
+    def _graph_capture(self, samples):
         dev = self.device
         from .data.packed import PackedBertBatch
-        sig = self._sig(sample)
-        self._g_raw = None
-        if isinstance(sample, PackedBertBatch):
-            from .ops import kernels as _k
-            self._g_raw, self._g_raw_dims = sample.raw.to(dev).clone(), sample.dims
-            self._g_sample = _k.assemble_bert_batch(self._g_raw, *self._g_raw_dims)
-            sample = self._g_sample
-        elif isinstance(sample, dict):
-            self._g_sample = {k: (v.to(dev).clone() if torch.is_tensor(v) else v) for k, v in sample.items()}
-        else:
-            self._g_sample = [t.to(dev).clone() for t in sample]
+        from .ops import kernels as _k
+        from .ops import native
+        sig = self._sig(samples)
+        st = {"samples": [], "raw": [], "raw_dims": []}
+        ss_sum = ns_sum = ntok_sum = 0.0
+        for sample in samples:
+            if isinstance(sample, PackedBertBatch):
+                raw, dims = sample.raw.to(dev).clone(), sample.dims
+                static = _k.assemble_bert_batch(raw, *dims)
+            elif isinstance(sample, dict):
+                raw, dims = None, None
+                static = {k: (v.to(dev).clone() if torch.is_tensor(v) else v) for k, v in sample.items()}
+            else:
+                raw, dims = None, None
+                static = [t.to(dev).clone() for t in sample]
+            st["samples"].append(static); st["raw"].append(raw); st["raw_dims"].append(dims)
+            ss = float(self.task._sample_size(static))
+            nt = float(self.task._num_tokens(static))
+            ns = float(self.task._num_sentences(static)) if hasattr(self.task, "_num_sentences") else ss
+            ss_sum += ss; ns_sum += ns; ntok_sum += nt
         if self._g_hyper is None:           # shared by every captured shape
             self._g_hyper = torch.zeros(4, dtype=torch.float32, device=dev)
             self._g_hyper_host = torch.zeros(4, dtype=torch.float32).pin_memory()
             self._g_out = torch.zeros(self._mailbox.FIELDS, dtype=torch.float64, device=dev)
             self._graph_pool = torch.cuda.graph_pool_handle()
-        ss = self.task._sample_size(sample)
-        ntok = self.task._num_tokens(sample)
-        self._g_const = torch.tensor([float(ss), float(ss), float(ntok)], dtype=torch.float32, device=dev)
+        st["const"] = torch.tensor([ss_sum, ns_sum, ntok_sum], dtype=torch.float32, device=dev)
+        st["const_last"] = torch.tensor([ss, ns, nt], dtype=torch.float32, device=dev)
+        st["last_loss"] = torch.zeros(1, dtype=torch.float32, device=dev)
         self._stage_hyper()
         torch.cuda.synchronize()
         # capture on a side stream, as torch requires; state changes made while capturing are real work that is
         # NOT executed (capture only records), so the first real execution is the first replay below
-        from .ops import native
         g = torch.cuda.CUDAGraph()
         self._model.train()
         before = native.launch_count()
         with torch.cuda.graph(g, pool=self._graph_pool):      # replays are serial, so all shapes share one pool
-            self._graph_body()
-        self._graph_launches = native.launch_count() - before      # kernels of ours inside one replay
-        native.add_launch_count(-self._graph_launches)              # capture recorded them, it did not run them
+            self._graph_body(st)
+        st["launches"] = native.launch_count() - before        # kernels of ours inside one replay
+        native.add_launch_count(-st["launches"])                # capture recorded them, it did not run them
+        st["graph"] = g
         self._graph = g
-        self._graph_sig = sig
-        self._graph_cache[sig] = {"graph": g, "sample": self._g_sample, "raw": self._g_raw,
-                                  "raw_dims": getattr(self, "_g_raw_dims", None), "const": self._g_const,
-                                  "launches": self._graph_launches}
+        self._graph_cache[sig] = st
         self._settle_gc(again=True)
-        print("| captured the training step in a CUDA graph (#{}: {} tensors, sample size {})".format(
-            len(self._graph_cache), len(sample), ss))
+        print("| captured the training step in a CUDA graph (#{}: {} micro-batch(es), sample size {})".format(
+            len(self._graph_cache), len(samples), ss_sum))
+        return st
 
     def _stage_hyper(self):
         opt = self.optimizer.optimizer
@@ -547,38 +654,43 @@ class Controller:
             self._g_hyper_host[i] = v
         self._g_hyper.copy_(self._g_hyper_host, non_blocking=True)
 
-    def _graph_train_step(self, sample):
+    def _graph_train_step(self, samples):
         self.meters["train_wall"].start()
         self._set_seed()
-        sig = self._sig(sample)
-        st = self._graph_cache.get(sig)
+        st = self._graph_cache.get(self._sig(samples))
         if st is None:
-            self._graph_capture(sample)
-        elif sig != self._graph_sig:         # switch to the graph captured for this batch shape
-            self._graph, self._g_sample, self._g_raw, self._g_raw_dims = st["graph"], st["sample"], st["raw"], st["raw_dims"]
-            self._g_const, self._graph_launches, self._graph_sig = st["const"], st["launches"], sig
-        if self._g_raw is not None:
-            self._g_raw.copy_(sample[0], non_blocking=True)
-        elif isinstance(sample, dict):
-            for k, src in sample.items():
-                if torch.is_tensor(src):
-                    self._g_sample[k].copy_(src, non_blocking=True)
-        else:
-            for dst, src in zip(self._g_sample, sample):
-                dst.copy_(src, non_blocking=True)
+            st = self._graph_capture(samples)
+        self._graph = st["graph"]
+        self._g_raw = st["raw"][0]
+        for i, sample in enumerate(samples):
+            static = st["samples"][i]
+            if st["raw"][i] is not None:
+                st["raw"][i].copy_(sample[0], non_blocking=True)
+            elif isinstance(sample, dict):
+                for k, src in sample.items():
+                    if torch.is_tensor(src):
+                        static[k].copy_(src, non_blocking=True)
+            else:
+                for dst, src in zip(static, sample):
+                    dst.copy_(src, non_blocking=True)
         self._stage_hyper()
-        self._graph.replay()
+        st["graph"].replay()
         from .ops import native
-        native.add_launch_count(self._graph_launches)
+        native.add_launch_count(st["launches"])
         opt = self.optimizer.optimizer
         opt._global_step += 1
-        self.set_num_updates(self.get_num_updates() + 1)
-        self.task.update_step(self._num_updates)
-        self._mailbox.post(self._g_out)
-        self._consume_stats(keep_latest=1 if self._lazy_stats else 0)
-        self.meters["train_wall"].stop()
-        return self._last_logging_output if self._last_logging_output is not None else {
-            "loss": 0.0, "nll_loss": 0.0, "ntokens": 0, "nsentences": 0, "sample_size": 0}
+        return self._finish_step(self._g_out)
+
+    def watchdog_report(self) -> Optional[str]:
+        """What the peer-to-peer kernels' watchdog recorded (which rank never arrived), or None.  The word lives in
+        mapped host memory: reading it needs no device call."""
+        red = self._reducer
+        if red is not None and hasattr(red, "watchdog_report"):
+            try:
+                return red.watchdog_report()
+            except Exception:
+                return None
+        return None
 
     def _prev_grad_norm_host(self):
         return self._prev_grad_norm

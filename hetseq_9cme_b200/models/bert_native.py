@@ -404,7 +404,9 @@ class PretrainLossFn(torch.autograd.Function):
         gemm(dup, first, a_mn=True, b_mn=True, out=_mg(pw), **wg)
         dfirst = gemm(dup, pw, b_mn=True)
         dseq.view(B, L, -1)[:, 0] += dfirst
-        nctx.sink.ready([p for p in heads.parameters()] + [pw, pb])
+        # the decoder weight is the word-embedding table (tied): its gradient is final only after the embedding
+        # backward has scattered the token-lookup part into it, so EmbeddingsFn.backward announces it, not this block
+        nctx.sink.ready([p for p in heads.parameters() if p is not emb_w] + [pw, pb])
         return dseq, None, None, None, None, None, None, None
 
 

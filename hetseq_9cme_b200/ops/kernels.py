@@ -185,12 +185,16 @@ def sumsq(g: torch.Tensor, out: torch.Tensor, accumulate: bool = False, ws: Opti
     return out
 
 
-def adam_flat(p, g, m, v, n, *, lr, beta1, beta2, eps, weight_decay, step, grad_scale_mult=1.0, max_norm=0.0,
-              norm_sq=None, sample_size=None, stats_out=None, zero_grad=True, p_bf16=None, hyper_dev=None):
+def make_adam_args(*, lr, beta1, beta2, eps, weight_decay, step, grad_scale_mult=1.0, max_norm=0.0, norm_sq=None,
+                   sample_size=None, stats_out=None, zero_grad=True, hyper_dev=None) -> AdamArgs:
     ss64 = sample_size if (sample_size is not None and sample_size.dtype == torch.float64) else None
     ss32 = sample_size if (sample_size is not None and sample_size.dtype == torch.float32) else None
-    a = AdamArgs(lr, beta1, beta2, eps, weight_decay, int(step), grad_scale_mult, max_norm, _ptr(norm_sq), _ptr(ss64),
-                 _ptr(stats_out), int(zero_grad), _ptr(ss32), _ptr(hyper_dev))
+    return AdamArgs(lr, beta1, beta2, eps, weight_decay, int(step), grad_scale_mult, max_norm, _ptr(norm_sq), _ptr(ss64),
+                    _ptr(stats_out), int(zero_grad), _ptr(ss32), _ptr(hyper_dev))
+
+
+def adam_flat(p, g, m, v, n, *, p_bf16=None, **kw):
+    a = make_adam_args(**kw)
     check(_lib().b200_adam_flat(p.data_ptr(), g.data_ptr(), m.data_ptr(), v.data_ptr(), _ptr(p_bf16), int(n), byref(a),
                                 _stream()), "b200_adam_flat")
 

@@ -172,6 +172,26 @@ class Adam(_ArenaMixin, torch.optim.Optimizer):
         if advance:
             self.mark_step()
 
+    def sharded_step(self, reducer, *, grad_scale_mult: float = 1.0, max_norm: float = 0.0, norm_sq=None, sample_size=None,
+                     stats_out=None, hyper_dev=None, advance: bool = True):
+        """The same update restricted to the arena slices this rank owns, with the new parameters written into every
+        rank by the kernel itself (``parallel/p2p.py``); moments of slices owned elsewhere are not maintained here —
+        ``reducer.gather_sharded`` makes them whole before a checkpoint."""
+        from .ops import kernels
+        g = self.param_groups[0]
+        if advance:
+            self._global_step += 1
+        args = kernels.make_adam_args(lr=g["lr"], beta1=g["betas"][0], beta2=g["betas"][1], eps=g["eps"],
+                                      weight_decay=g["weight_decay"], step=max(self._global_step, 1),
+                                      grad_scale_mult=grad_scale_mult, max_norm=max_norm, norm_sq=norm_sq,
+                                      sample_size=sample_size, stats_out=stats_out, zero_grad=True, hyper_dev=hyper_dev)
+        reducer.sharded_adam(args, self._flat_state["exp_avg"], self._flat_state["exp_avg_sq"])
+        if advance:
+            self.mark_step()
+
+    def flat_state_tensors(self):
+        return [self._flat_state[n] for n in self._state_names] if self.has_arena else []
+
     def mark_step(self):
         for p in self.arena.params:
             self.state[p]["step"] = self._global_step

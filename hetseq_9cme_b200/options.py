@@ -197,15 +197,21 @@ _ENGINE = [
                                 help="bucket size of the peer-to-peer reducer (--bucket-cap-mb keeps applying to the "
                                      "torch.distributed reducer); 0: use --bucket-cap-mb")),
     (("--no-native",), dict(action="store_true", help="force the plain-PyTorch model path (CPU/debug only)")),
-    (("--cuda-graph",), dict(action="store_true", help="capture the fixed-shape train step in a CUDA graph")),
+    (("--cuda-graph",), dict(action=argparse.BooleanOptionalAction, default=None,
+                             help="capture the train step (all micro-batches of an update) in a CUDA graph per batch "
+                                  "shape and replay it; default: on when training on CUDA")),
+    (("--no-sharded-optimizer",), dict(action="store_true",
+                                       help="peer-to-peer reducer: all-reduce the gradients and run the optimizer "
+                                            "replicated on every rank instead of reduce-scatter + owned-slice update + "
+                                            "parameter broadcast")),
     (("--checkpoint-activations",), dict(action="store_true", help="recompute encoder activations in backward")),
     (("--pad-to-multiple-of",), dict(type=int, default=0, metavar="N",
                                      help="NER / EL collators: pad the batch width up to a multiple of N (0: longest "
                                           "sequence, as the reference); with --cuda-graph this bounds the number of "
                                           "distinct batch shapes, i.e. of captured graphs")),
-    (("--device-batch-assembly",), dict(action="store_true",
+    (("--device-batch-assembly",), dict(action=argparse.BooleanOptionalAction, default=None,
                                         help="ship BERT batches as one packed int32 matrix and build the int64 inputs / "
-                                             "dense MLM labels with a kernel on the GPU")),
+                                             "dense MLM labels with a kernel on the GPU; default: on when training on CUDA")),
     (("--max-predictions-per-seq",), dict(type=int, default=0, metavar="P",
                                           help="upper bound of masked positions per sequence (0: sequence length)")),
     (("--profile",), dict(action="store_true", help="emit NVTX ranges per phase")),
@@ -306,7 +312,21 @@ def parse_args_and_arch(parser, s=None):
         args.max_sentences_valid = getattr(args, "max_sentences", None)
     if getattr(args, "max_tokens_valid", None) is None:
         args.max_tokens_valid = getattr(args, "max_tokens", None)
+    # engine switches that default to "on when the step runs on a GPU"
+    for name in ("cuda_graph", "device_batch_assembly"):
+        if hasattr(args, name) and getattr(args, name) is None:
+            setattr(args, name, _on_cuda(args))
     return args
+
+
+def _on_cuda(args) -> bool:
+    if getattr(args, "cpu", False) or getattr(args, "no_native", False) or getattr(args, "precision", "tf32") == "fp32":
+        return False
+    try:
+        import torch
+        return bool(torch.cuda.is_available())
+    except Exception:
+        return False
 
 
 def parse_training_args(argv: Optional[Sequence[str]] = None):

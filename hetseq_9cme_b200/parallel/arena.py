@@ -31,7 +31,7 @@ def _round_up(n: int, a: int = ALIGN) -> int:
 class ParamArena:
     def __init__(self, params: Sequence[torch.nn.Parameter], groups: Optional[Iterable[Sequence[torch.nn.Parameter]]] = None,
                  device=None, compute_dtype: torch.dtype = torch.float32, bucket_bytes: int = 25 * 1024 * 1024,
-                 grad_alloc=None):
+                 grad_alloc=None, alloc=None):
         params = [p for p in params if p.requires_grad]
         seen = set()
         uniq = []
@@ -70,12 +70,22 @@ class ParamArena:
             self.offsets[id(p)] = off
             off += _round_up(p.numel())
         self.numel = off
-        self.master = torch.zeros(off, dtype=torch.float32, device=self.device)
+        # ``alloc(kind, numel, dtype)`` lets the reducer place an arena in memory it can share with the peers (symmetric
+        # buffers of the communication runtime): kind is 'grad', 'master' or 'work'; None -> ordinary device memory
+        def _place(kind, numel, dtype):
+            t = alloc(kind, numel, dtype) if alloc is not None else None
+            if t is None:
+                return torch.zeros(numel, dtype=dtype, device=self.device)
+            t.zero_()
+            return t
+        self.master = _place("master", off, torch.float32)
         # 64 spare floats behind the gradients: the per-step statistics vector lives there so that it can ride the
         # same peer-memory mapping / reducer as the gradient buckets
         # (``grad_alloc(numel)`` lets the reducer supply memory it can share with peers, e.g. a symmetric allocation)
         self._grad_full = None
-        if grad_alloc is not None:
+        if alloc is not None:
+            self._grad_full = alloc("grad", off + ALIGN, torch.float32)
+        elif grad_alloc is not None:
             self._grad_full = grad_alloc(off + ALIGN)
         if self._grad_full is None:
             self._grad_full = torch.zeros(off + ALIGN, dtype=torch.float32, device=self.device)
@@ -83,7 +93,7 @@ class ParamArena:
             self._grad_full.zero_()
         self.grad = self._grad_full[:off]
         self.tail = self._grad_full[off:]
-        self.work = torch.zeros(off, dtype=torch.bfloat16, device=self.device) if compute_dtype == torch.bfloat16 else None
+        self.work = _place("work", off, torch.bfloat16) if compute_dtype == torch.bfloat16 else None
 
         with torch.no_grad():
             for p in order:

@@ -37,6 +37,7 @@ class BaseReducer(GradSink):
         self._seen = set()
         self._after_backward = False
         self.fused_norm = False           # True: reductions leave sum(g^2) in arena.tail (no separate norm pass)
+        self.sharded = False              # True: reduce-scatter only; the optimizer step runs on owned slices (p2p.py)
 
     # ---- step protocol ---------------------------------------------------------------------------
     def begin(self, sync_now: bool):
@@ -105,6 +106,9 @@ class BaseReducer(GradSink):
         if self.world_size > 1:
             dist.all_reduce(self.arena.tail)
 
+    def gather_sharded(self, flats) -> None:
+        """Sharded back ends make tensors whose slices only their owners keep current whole again (checkpoints)."""
+
     def broadcast_parameters(self):
         """Make every rank start from rank 0's parameters (what DDP does at construction)."""
         if self.world_size > 1:
@@ -152,17 +156,25 @@ class NullReducer(BaseReducer):
         pass
 
 
-def build_reducer(args, arena, world_size: int):
+def build_reducer(args, arena, world_size: int, sharded: bool = False):
+    """Pick the back end.  Every rank must end up with the SAME kind of reducer (they issue different collectives),
+    so a failure on one rank is agreed on by all before anyone falls back."""
     if world_size <= 1:
         return NullReducer(arena, 1)
     comm = getattr(args, "comm", "auto")
     if arena.device.type == "cuda" and comm in ("auto", "p2p"):
+        from . import p2p
+        red, err = None, None
         try:
-            from .p2p import P2PReducer
-            return P2PReducer(arena, world_size)
+            red = p2p.P2PReducer(arena, world_size, sharded=sharded)
         except Exception as e:  # peer access unavailable (multi-node, MIG, ...) -> documented fallback
-            if comm == "p2p":
-                raise
-            from ..distributed_utils import log_all
-            log_all("| p2p reducer unavailable ({}); using torch.distributed all-reduce".format(e))
+            err = e
+        if p2p._all_ranks_ok(red is not None):
+            return red
+        if red is not None:
+            red.close()
+        if comm == "p2p":
+            raise RuntimeError("--comm p2p: the peer-to-peer reducer could not be set up on every rank ({})".format(err or "peer failure"))
+        from ..distributed_utils import log_all
+        log_all("| p2p reducer unavailable ({}); using torch.distributed all-reduce".format(err or "a peer rank failed"))
     return TorchReducer(arena, world_size)

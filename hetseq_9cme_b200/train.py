@@ -101,7 +101,17 @@ def train(args, controller, task, epoch_itr):
     valid_subsets = args.valid_subset.split(",")
     max_update = args.max_update or math.inf
     for i, samples in enumerate(progress, start=epoch_itr.iterations_in_epoch):
-        log_output = controller.train_step(samples)
+        try:
+            log_output = controller.train_step(samples)
+        except RuntimeError:
+            # a peer that died (or stalled past B200_P2P_TIMEOUT_S) trips the reduction kernels' watchdog: say which
+            # rank went missing and leave with a distinct exit code instead of hanging in the next collective
+            report = controller.watchdog_report()
+            if report:
+                distributed_utils.log_all("| FATAL (rank {}): {}".format(getattr(args, "distributed_rank", 0), report))
+                sys.stdout.flush()
+                os._exit(86)
+            raise
         if log_output is None:
             continue
         stats = get_training_stats(controller)

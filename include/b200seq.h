@@ -274,6 +274,56 @@ int b200_p2p_allreduce(void* const* data_ptrs, void* const* flag_ptrs, void* cou
                        void* multicast_base /* optional NVLS multicast address of the arena: multimem.ld_reduce / .st */,
                        void* stream);
 
+/* Reduce-scatter half of the above (sharded-optimizer mode): the SUM over ranks of this rank's 1/world slice of
+ * arena[start, start+n) is written into the LOCAL arena only (plus sum of squares into sq_out); nothing is sent
+ * back.  One flag round per bucket: a later collective on the same ranks (b200_p2p_allreduce of the statistics
+ * tail) is what tells a rank that its peers are done reading its gradients.  Slice r of a bucket covers float4
+ * indices [r*per, min((r+1)*per, n/4)) with per = ceil(n/4 / world) — b200_p2p_sharded_adam uses the same rule. */
+int b200_p2p_reduce_scatter(void* const* data_ptrs, void* const* flag_ptrs, void* counter, int rank, int world,
+                            long long start, long long n, int bucket, int max_buckets, void* epoch_dev, int blocks,
+                            float* sq_out, void* multicast_base, void* stream);
+
+/* Optimizer step of the sharded mode — the fused reduce -> scale/clip -> Adam -> parameter broadcast path
+ * (ref: hetseq/controller.py:338-347 multiply_grads / clip_grad_norm / optimizer.step, hetseq/optim.py:206-229).
+ * Each rank applies the reference Adam update to ITS slice of every bucket (ranges[2*b], ranges[2*b+1] = start and
+ * length of bucket b in elements, device array, n_buckets entries) using its local, already reduced gradient, and
+ * writes the new parameters into every rank's copy: fp32 masters through param_ptrs / param_mc when bf16_ptrs is
+ * null, otherwise the fp32 master stays local (only the owner's slice is kept current) and the bf16 working copy
+ * is what travels (bf16_ptrs / bf16_mc).  It also zeroes the whole local gradient arena [0, total).  A flag round
+ * (slot `bucket`) ends the kernel: when it retires every peer's writes into this rank's parameters have landed.
+ * Scalars as in b200_adam_flat (a->norm_sq / sample_size / hyper_dev / stats_out). */
+int b200_p2p_sharded_adam(void* const* param_ptrs, void* param_mc, void* const* bf16_ptrs, void* bf16_mc,
+                          float* grad, float* m, float* v, const long long* ranges, int n_buckets, long long total,
+                          void* const* flag_ptrs, void* counter, int rank, int world, int bucket, int max_buckets,
+                          void* epoch_dev, const b200_adam_args* a, int blocks, void* stream);
+
+/* How long a kernel waits for a peer's flag before it gives up (seconds; default 600), and an optional word of
+ * mapped pinned host memory that then receives (0x80000000 | slot << 8 | missing rank).  A tripped watchdog does
+ * not trap: the kernel finishes on incomplete data, later waits return immediately, and the host is expected to
+ * check the word after each step and stop.  b200_p2p_watchdog_reset clears the tripped state (tests). */
+int b200_p2p_set_watchdog(double timeout_seconds, unsigned int* host_error_word_devptr);
+int b200_p2p_watchdog_reset(void);
+
+/* ------------------------------------------------------------------------------------------------
+ * Communication runtime (csrc/comm_runtime.cu): rendezvous over Unix sockets, symmetric buffers from the CUDA
+ * virtual-memory API mapped into every rank, NVLS multicast mappings.  Replaces what the reference gets from
+ * torch.distributed's process group + DDP's bucket allocation (hetseq/distributed_utils.py:11-41,
+ * hetseq/controller.py:79-87).  One NVSwitch domain, <= 8 ranks, one process per GPU, device current at init.
+ * ---------------------------------------------------------------------------------------------- */
+typedef struct {
+  void* handle;        /* pass to b200_comm_free */
+  long long bytes;     /* mapped size (>= requested, rounded to the allocation granularity) */
+  void* local;         /* this rank's buffer, zero-filled */
+  void* peer[8];       /* rank r's buffer as mapped in this process (peer[rank] == local) */
+  void* multicast;     /* NVLS address covering all ranks' buffers, or NULL */
+} b200_comm_buffer;
+int b200_comm_init(int rank, int world, const char* tag, int timeout_ms, void** comm_out);
+int b200_comm_multicast_supported(void* comm);
+int b200_comm_barrier(void* comm);
+int b200_comm_alloc(void* comm, long long bytes, int want_multicast, b200_comm_buffer* out);   /* collective */
+int b200_comm_free(void* comm, void* handle);
+int b200_comm_destroy(void* comm);
+
 #ifdef __cplusplus
 }
 #endif

@@ -36,7 +36,7 @@ def _setup(tmp_path, extra):
 
 
 def test_cuda_graph_step_matches_eager(tmp_path):
-    eager, it1 = _setup(tmp_path, [])
+    eager, it1 = _setup(tmp_path, ["--no-cuda-graph"])
     graph, it2 = _setup(tmp_path, ["--cuda-graph"])
     for _ in range(8):
         eager.train_step([next(it1)])
@@ -53,7 +53,7 @@ def test_cuda_graph_step_matches_eager(tmp_path):
 def test_fused_step_matches_per_tensor_reference_math(tmp_path):
     """One Controller step on the GPU (fused scale/clip/Adam on the arena) against the same step computed with the
     plain-PyTorch model path and the per-tensor optimizer code."""
-    c, it = _setup(tmp_path, [])
+    c, it = _setup(tmp_path, ["--no-cuda-graph", "--no-device-batch-assembly"])
     ref, it_ref = _setup(tmp_path, ["--no-native", "--precision", "fp32", "--cpu"])
     # identical initial weights
     ref.get_model().load_state_dict({k: v.cpu() for k, v in c.get_model().state_dict().items()})
@@ -95,8 +95,8 @@ def test_device_batch_assembly_kernel_and_step(tmp_path):
     for a, b in zip(got, want):
         assert a.dtype == torch.int64 and torch.equal(a.cpu(), b)
 
-    plain, it1 = _setup(tmp_path, [])
-    packed, it2 = _setup(tmp_path, ["--device-batch-assembly"])
+    plain, it1 = _setup(tmp_path, ["--no-cuda-graph", "--no-device-batch-assembly"])
+    packed, it2 = _setup(tmp_path, ["--no-cuda-graph", "--device-batch-assembly"])
     graph, it3 = _setup(tmp_path, ["--device-batch-assembly", "--cuda-graph"])
     from hetseq_9cme_b200.data.packed import PackedBertBatch
     for _ in range(7):
@@ -138,7 +138,7 @@ def test_cuda_graph_cache_handles_several_batch_shapes(tmp_path):
         c.lr_step(it.epoch)
         return c, it.next_epoch_itr(shuffle=False)
 
-    eager, it1 = build([])
+    eager, it1 = build(["--no-cuda-graph"])
     graph, it2 = build(["--cuda-graph"])
     widths = set()
     for _ in range(30):

@@ -26,6 +26,45 @@ def _unavailable(why):
     return 0
 
 
+_CONLL_TAGS = ["O", "B-PER", "I-PER", "B-ORG", "I-ORG", "B-LOC", "I-LOC", "B-MISC", "I-MISC"]
+
+
+def install_conll_loader():
+    """The reference's NER task calls ``datasets.load_dataset(<loading script>, data_files=...)``
+    (hetseq/tasks/bert_for_token_classification_task.py:44).  The ``datasets`` release on this image no longer runs
+    loading scripts, so — like the h5py stand-in — the harness supplies what the dependency cannot: a
+    ``load_dataset`` that reads the CoNLL-2003 column files into the same DatasetDict (``tokens`` + ``ner_tags`` as
+    a ClassLabel sequence).  Reference code is untouched; it keeps doing its own tokenisation, label alignment,
+    collation and batching on the result."""
+    import datasets
+
+    def read(path):
+        toks, tags, rows = [], [], {"id": [], "tokens": [], "ner_tags": []}
+        with open(path) as f:
+            for line in f:
+                line = line.strip()
+                if not line or line.startswith("-DOCSTART-"):
+                    if toks:
+                        rows["id"].append(str(len(rows["id"]))); rows["tokens"].append(toks); rows["ner_tags"].append(tags)
+                        toks, tags = [], []
+                    continue
+                parts = line.split()
+                toks.append(parts[0]); tags.append(_CONLL_TAGS.index(parts[-1]))
+        if toks:
+            rows["id"].append(str(len(rows["id"]))); rows["tokens"].append(toks); rows["ner_tags"].append(tags)
+        return rows
+
+    feats = datasets.Features({"id": datasets.Value("string"), "tokens": datasets.Sequence(datasets.Value("string")),
+                               "ner_tags": datasets.Sequence(datasets.ClassLabel(names=_CONLL_TAGS))})
+
+    def load_dataset(path=None, data_files=None, **kwargs):
+        return datasets.DatasetDict({split: datasets.Dataset.from_dict(read(fn), features=feats) for split, fn in (data_files or {}).items()})
+
+    datasets.load_dataset = load_dataset
+    # datasets' torch formatter imports torchvision.io.VideoReader, which this image's torchvision no longer has
+    datasets.config.TORCHVISION_AVAILABLE = False
+
+
 def run_reference(a):
     if not os.path.isdir(os.path.join(REF, "hetseq")):
         return _unavailable("baseline/_ref is missing (pip install --no-deps --target baseline/_ref /root/reference)")
@@ -61,20 +100,39 @@ def run_reference(a):
         nsteps_needed = 2 * a.steps + a.warmup + 8       # fp32 pass + TF32 companion pass
         per_rank = nsteps_needed * a.batch
         max_pred = 20 if a.seq_len <= 128 else 80
-        n_per_file = (per_rank * world + 1) // 2 + a.batch
-        for i in range(2):
-            arrs = synthetic.bert_shard_arrays(n_per_file, a.seq_len, max_pred, 30522, 1234 + i)
-            np.savez(os.path.join(tmp, "train_shard_%d.npz" % i), **arrs)
-        np.savez(os.path.join(tmp, "test_shard_0.npz"), **synthetic.bert_shard_arrays(a.batch, a.seq_len, max_pred, 30522, 2234))
-        cfg_path = synthetic.write_bert_config(os.path.join(tmp, "bert_config.json"), **MODELS[a.model])
         vocab_path = synthetic.write_vocab(os.path.join(tmp, "vocab.txt"))
-        argv = ["--data", tmp, "--dict", vocab_path, "--config_file", cfg_path, "--max-sentences", str(a.batch),
-                "--max-epoch", "1000", "--lr", "1e-4", "--warmup-updates", "100", "--total-num-update", "100000",
-                "--weight-decay", "0.01", "--clip-norm", "25", "--fast-stat-sync", "--valid-subset", "test", "--num-workers", "4",
-                "--save-dir", os.path.join(tmp, "ckpt"), "--no-save", "--log-format", "none",
-                "--distributed-world-size", str(world)]
-        parser = options.get_training_parser(task="bert", optimizer="adam", lr_scheduler="PolynomialDecayScheduler")
+        common = ["--max-sentences", str(a.batch), "--max-epoch", "1000", "--lr", "1e-4", "--warmup-updates", "100",
+                  "--total-num-update", "100000", "--weight-decay", "0.01", "--clip-norm", "25", "--fast-stat-sync",
+                  "--valid-subset", "test", "--save-dir", os.path.join(tmp, "ck"), "--no-save", "--log-format", "none",
+                  "--distributed-world-size", str(world)]
+        if getattr(a, "task", "bert") == "ner":
+            # BASELINE config 5: token classification on CoNLL-2003-shaped text, the reference's own task / collator /
+            # dataset wrapper (hetseq/tasks/bert_for_token_classification_task.py:189-228); same corpus as our arm
+            install_conll_loader()
+            import importlib
+            paths = synthetic.make_conll(tmp, n_train=per_rank * world + a.batch, n_valid=a.batch, n_test=a.batch,
+                                         vocab_words=20000, seed=1234)
+            cfg_path = synthetic.write_bert_config(os.path.join(tmp, "bert_config.json"), vocab_size=20005, **MODELS[a.model])
+            argv = ["--data", tmp, "--dict", paths["vocab"], "--config_file", cfg_path, "--train_file", paths["train"],
+                    "--validation_file", paths["validation"], "--test_file", paths["test"], "--extension_file", "conll2003",
+                    "--num-workers", "2"] + common
+            parser = options.get_training_parser(task="BertForTokenClassification", optimizer="adam",
+                                                 lr_scheduler="PolynomialDecayScheduler")
+            task_cls = importlib.import_module("hetseq.tasks.bert_for_token_classification_task").BertForTokenClassificationTask
+            task_name = "BertForTokenClassification"
+        else:
+            n_per_file = (per_rank * world + 1) // 2 + a.batch
+            for i in range(2):
+                arrs = synthetic.bert_shard_arrays(n_per_file, a.seq_len, max_pred, 30522, 1234 + i)
+                np.savez(os.path.join(tmp, "train_shard_%d.npz" % i), **arrs)
+            np.savez(os.path.join(tmp, "test_shard_0.npz"), **synthetic.bert_shard_arrays(a.batch, a.seq_len, max_pred, 30522, 2234))
+            cfg_path = synthetic.write_bert_config(os.path.join(tmp, "bert_config.json"), **MODELS[a.model])
+            argv = ["--data", tmp, "--dict", vocab_path, "--config_file", cfg_path, "--num-workers", "4"] + common
+            parser = options.get_training_parser(task="bert", optimizer="adam", lr_scheduler="PolynomialDecayScheduler")
+            task_cls = tasks.LanguageModelingTask
+            task_name = "bert"
         args = options.parse_args_and_arch(parser, argv)
+        args.task = task_name
         args.device_id = local
         args.distributed_rank = rank
         np.random.seed(args.seed)
@@ -82,8 +140,9 @@ def run_reference(a):
         if world > 1:
             args.distributed_init_method = "env://"
             args.distributed_rank = distributed_utils.distributed_init(args)
-        task = tasks.LanguageModelingTask.setup_task(args)
-        task.load_dataset("test", combine=False, epoch=0)
+        task = task_cls.setup_task(args)
+        if task_name == "bert":
+            task.load_dataset("test", combine=False, epoch=0)
         model = task.build_model(args)
         controller = Controller(args, task, model)
         epoch_itr = controller.get_train_iterator(epoch=0, load_dataset=True)
@@ -108,7 +167,8 @@ def run_reference(a):
             e0.record()
             for _ in range(a.steps):
                 samples = next(itr)
-                h2d += sum(t.numel() * t.element_size() for t in samples[0])
+                first = samples[0]
+                h2d += sum(t.numel() * t.element_size() for t in (first.values() if isinstance(first, dict) else first) if torch.is_tensor(t))
                 controller.train_step(samples)
             e1.record()
             sync_all()

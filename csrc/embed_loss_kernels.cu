@@ -663,10 +663,20 @@ extern "C" long long b200_colsum_scratch_bytes(int rows, int cols) {
   return (long long)parts * cols * 4;
 }
 
+// vector loads in the column-sum kernels fetch 4 elements at once: base and pitch must keep every row 16-byte
+// (fp32) / 8-byte (bf16) aligned and the pitch must cover a row
+static int colsum_check_layout(const char* who, int dtype, const void* x, long long ldx, int cols) {
+  const uintptr_t align = dtype == 0 ? 16 : 8;
+  if ((reinterpret_cast<uintptr_t>(x) & (align - 1)) != 0) return fail(B200_ERR_ARG, "%s: x must be %d-byte aligned", who, (int)align);
+  if (ldx < cols || (ldx & 3)) return fail(B200_ERR_ARG, "%s: row pitch %lld must be a multiple of 4 elements and >= cols (%d)", who, ldx, cols);
+  return 0;
+}
+
 extern "C" int b200_colsum(int dtype, const void* x, long long ldx, int rows, int cols, float* out, void* scratch,
                            long long scratch_bytes, void* stream) {
   if (!x || !out) return fail(B200_ERR_ARG, "colsum: null pointer");
   if (cols & 3) return fail(B200_ERR_UNSUPPORTED, "colsum: cols must be a multiple of 4");
+  if (const int lrc = colsum_check_layout("colsum", dtype, x, ldx, cols)) return lrc;
   const int parts = rows >= 2048 ? 64 : (rows >= 256 ? 16 : 1);
   if (scratch == nullptr) {
     // no scratch given: one kernel, partial sums added to out[] with fp32 reductions (summation order varies)
@@ -772,6 +782,7 @@ extern "C" int b200_colsum_static(int dtype, const void* x, long long ldx, int r
   if (cols > kStaticColsumMaxCols)
     return fail(B200_ERR_ARG, "colsum_static: cols = %d exceeds the built-in scratch (max %d columns); use b200_colsum with your own scratch",
                 cols, kStaticColsumMaxCols);
+  if (const int lrc = colsum_check_layout("colsum_static", dtype, x, ldx, cols)) return lrc;
   float* scratch = nullptr;
   const int rc = colsum_static_scratch(&scratch);
   if (rc) return rc;

@@ -376,6 +376,11 @@ class BertPreTrainedModel(nn.Module):
         from .models import bert_native
         why = bert_native.native_supported(self.config, input_ids.size(1))
         if why is not None:
+            # an arena-bound model on a GPU is expected to run the sm_100a kernels: dropping a whole model to eager
+            # PyTorch must be the user's explicit choice (--no-native / force_torch_path), never a quiet side effect
+            if not getattr(self, "allow_torch_fallback", False):
+                raise RuntimeError("the native kernels do not cover this model ({}); pass --no-native to run it on the "
+                                   "plain PyTorch path".format(why))
             if not self._native_notice:
                 print("| native kernels disabled for this model: {}".format(why), flush=True)
                 self._native_notice = True

@@ -400,8 +400,18 @@ class Controller:
                 host_stats[1] += logging_output.get("nsentences", 0)
                 host_stats[2] += logging_output.get("ntokens", 0)
                 on_loss(logging_output)
+                self._note_mlm_overflow()
                 last_logging, last_sample_size = logging_output, sample_size
         return host_stats, last_logging, last_sample_size
+
+    def _note_mlm_overflow(self):
+        """The labelled-positions MLM head has a fixed capacity; positions beyond it are dropped.  Their count rides
+        the statistics mailbox (field 7, no sync) and turns into a warning when the host reads it."""
+        cnt = getattr(self._model, "last_mlm_count", None)
+        if cnt is not None and self.cuda:
+            if getattr(self, "_mlm_over", None) is None:
+                self._mlm_over = torch.zeros(1, dtype=torch.float64, device=self.device)
+            self._mlm_over += (cnt[1] - cnt[0]).clamp_min(0).double()
 
     def _device_update(self, tail, sample_size_dev, mult, hyper_dev=None, advance=True):
         """After backward: wait for the bucket reductions, reduce the statistics tail, then scale / clip / update in
@@ -475,6 +485,9 @@ class Controller:
             stat_sum[2:5] = torch.tensor([float(last_sample_size), float(ll.get("nsentences", 0)), float(ll.get("ntokens", 0))],
                                          dtype=torch.float64).to(dev, non_blocking=True)
         stat_sum[5:7] = step_stats[0:3:2].double()
+        if getattr(self, "_mlm_over", None) is not None:
+            stat_sum[7:8] = self._mlm_over
+            self._mlm_over.zero_()
         return self._finish_step(stat_sum)
 
     def _eager_step_cpu(self, samples, dummy_batch):
@@ -582,6 +595,7 @@ class Controller:
             lf = loss.detach().reshape(1).float()
             tail[0:1] += lf
             tail[1:2] += lf
+            self._note_mlm_overflow()
             if i == n - 1:
                 st["last_loss"].copy_(lf)
         tail[2:5] += st["const"]
@@ -596,6 +610,9 @@ class Controller:
             self._g_out[0:2] = st["last_loss"].double().expand(2)
             self._g_out[2:5] = st["const_last"].double()
         self._g_out[5:7] = step_stats[0:3:2].double()
+        if getattr(self, "_mlm_over", None) is not None:
+            self._g_out[7:8] = self._mlm_over
+            self._mlm_over.zero_()
 
     def _graph_capture(self, samples):
         dev = self.device
@@ -698,6 +715,11 @@ class Controller:
     def _consume_stats(self, keep_latest: int):
         for v in self._mailbox.drain(keep_latest):
             loss, nll, sample_size, nsent, ntok, gnorm, clipped = (float(x) for x in v[:7])
+            if float(v[7]) > 0 and not getattr(self, "_warned_mlm_overflow", False):
+                self._warned_mlm_overflow = True
+                print("| WARNING: {:.0f} labelled MLM positions exceeded the head's capacity (--max-predictions-per-seq "
+                      "{}) and were left out of the loss; raise the flag".format(
+                          float(v[7]), getattr(self._model, "max_predictions_per_seq", "?")), flush=True)
             if self.fast_stat_sync and sample_size > 0:
                 # reference: global sums divided by sample_size and converted to base 2 (controller.py:298-305)
                 loss, nll = loss / (sample_size * _LN2), nll / (sample_size * _LN2)

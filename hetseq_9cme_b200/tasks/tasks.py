@@ -131,7 +131,13 @@ class LanguageModelingTask(Task):
         from ..bert_modeling import BertConfig, BertForPreTraining
         config = BertConfig.from_json_file(args.config_file)
         model = BertForPreTraining(config)
-        model.max_predictions_per_seq = getattr(args, "max_predictions_per_seq", 0) or getattr(self, "_max_pred", 0)
+        # capacity of the labelled-positions MLM head: never below the width of the shards' masked_lm_positions (a
+        # smaller flag would silently drop labels — e.g. "20" from a phase-1 script on phase-2 shards carrying 80)
+        flag, width = int(getattr(args, "max_predictions_per_seq", 0) or 0), int(getattr(self, "_max_pred", 0) or 0)
+        if flag and width and flag < width:
+            print("| WARNING: --max-predictions-per-seq {} is below the data's masked_lm_positions width {}; using {}".format(
+                flag, width, width))
+        model.max_predictions_per_seq = max(flag, width)
         model.checkpoint_activations = bool(getattr(args, "checkpoint_activations", False))
         return model
 

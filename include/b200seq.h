@@ -202,7 +202,9 @@ int b200_colsum(int dtype, const void* x, long long ldx, int rows, int cols, flo
  * call on each device resolves the array's device address (make that call before any stream capture begins).
  * All calls share the one array and it keeps the previous call's partials (none of them needs clearing: every
  * launch rewrites what it reads), so calls that may overlap on the GPU race — keep them on one stream or order
- * them with events. */
+ * them with events.  `stream` must belong to the device that is current at the call (the array's address is
+ * looked up for the current device).  As for b200_colsum, x must be 16-byte aligned for fp32 (8-byte for bf16)
+ * and ldx a multiple of 4 elements and >= cols; violations are refused with an error code. */
 int b200_colsum_static_max_cols(void);
 int b200_colsum_static(int dtype, const void* x, long long ldx, int rows, int cols, float* out, void* stream);
 

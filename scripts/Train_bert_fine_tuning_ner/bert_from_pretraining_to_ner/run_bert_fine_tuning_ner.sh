@@ -7,5 +7,5 @@ python3 ${DIST}/hetseq_9cme_b200/train.py \
   --train_file ${DATA:-$DIST/ner_data}/train.txt --validation_file ${DATA:-$DIST/ner_data}/valid.txt \
   --test_file ${DATA:-$DIST/ner_data}/test.txt --max-sentences 32 --fast-stat-sync --max-epoch 4 --update-freq 1 \
   --valid-subset test --num-workers 4 --warmup-updates 100 --total-num-update 2000 --lr 5e-5 --weight-decay 0.01 \
-  --cuda-graph --pad-to-multiple-of 8 --hetseq_state_dict ${CKPT:?set CKPT=checkpoint_last.pt} \
+  --pad-to-multiple-of 8 --hetseq_state_dict ${CKPT:?set CKPT=checkpoint_last.pt} \
   --distributed-world-size ${GPUS:-1} --save-dir bert_from_pretraining_to_ner 2>&1 | tee bert_from_pretraining_to_ner.log

@@ -158,8 +158,52 @@ def test_seqeval_lite_and_ner_eval(tmp_path):
             "--valid-subset", "test", "--save-dir", d + "/ck", "--max-epoch", "1", "--distributed-world-size", "1",
             "--num-workers", "0", "--log-format", "none"]
     train.main(options.parse_training_args(argv))
-    out = eval_bert_fine_tuning_ner.evaluate(d + "/ck/checkpoint_last.pt", cfg, paths["vocab"], paths["test"], device="cpu")
+    out = eval_bert_fine_tuning_ner.evaluate(d + "/ck/checkpoint_last.pt", cfg, paths["vocab"], paths["test"], device="cpu",
+                                             return_logits=True)
+    logits = out.pop("logits")
     assert set(out) == {"accuracy_score", "precision", "recall", "f1"} and 0.0 <= out["accuracy_score"] <= 1.0
+    # cross-implementation check (reference: test/TRANFORMERS_test_eval_bert_fine_tuning.py): the same checkpoint under
+    # Hugging Face's BertForTokenClassification gives the same logits, hence the same scores
+    pytest.importorskip("transformers")
+    hf = eval_bert_fine_tuning_ner.evaluate(d + "/ck/checkpoint_last.pt", cfg, paths["vocab"], paths["test"], device="cpu",
+                                            impl="transformers", return_logits=True)
+    for a_, b_ in zip(logits, hf.pop("logits")):
+        assert torch.allclose(a_, b_, atol=2e-4, rtol=1e-3), (a_ - b_).abs().max()
+    assert hf == out
+
+
+def test_transformers_task_variant_steps_through_the_controller(tmp_path):
+    """hetseq/transformers_tasks.py:395-477 counterpart: a Hugging Face BertForTokenClassification trained by this
+    engine (arena, fused step): the loss goes down and a checkpoint is written."""
+    pytest.importorskip("transformers")
+    from hetseq_9cme_b200 import options
+    from hetseq_9cme_b200.controller import Controller
+    from hetseq_9cme_b200.data import synthetic
+    from hetseq_9cme_b200.transformers_tasks import TransformersBertForTokenClassificationTask
+    d = str(tmp_path)
+    paths = synthetic.make_conll(d, n_train=64, n_valid=8, n_test=8, vocab_words=40)
+    cfg = synthetic.write_bert_config(os.path.join(d, "c.json"), vocab_size=45, **CFG)
+    argv = ["--task", "BertForTokenClassification", "--data", d, "--dict", paths["vocab"], "--config_file", cfg,
+            "--train_file", paths["train"], "--test_file", paths["test"], "--cpu", "--max-sentences", "8", "--lr", "3e-3",
+            "--valid-subset", "test", "--save-dir", d + "/ck", "--distributed-world-size", "1", "--num-workers", "0",
+            "--log-format", "none"]
+    args = options.parse_training_args(argv)
+    torch.manual_seed(0)
+    task = TransformersBertForTokenClassificationTask.setup_task(args)
+    model = task.build_model(args)
+    assert type(model).__module__.startswith("transformers")
+    c = Controller(args, task, model)
+    it = c.get_train_iterator(epoch=0, load_dataset=True)
+    c.lr_step(it.epoch)
+    losses = []
+    for epoch in range(3):
+        for s in it.next_epoch_itr(shuffle=False):
+            out = c.train_step([s])
+            losses.append(out["loss"])
+    c.flush_stats()
+    assert c.get_num_updates() == 24 and losses[-1] < 0.7 * losses[1]
+    c.save_checkpoint(d + "/hf.pt", {"train_iterator": it.state_dict()})
+    assert any(k.startswith("bert.encoder.layer.0.") for k in torch.load(d + "/hf.pt", weights_only=False)["model"])
 
 
 def test_file_utils_and_legacy_loader(tmp_path):

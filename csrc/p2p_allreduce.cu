@@ -39,6 +39,7 @@ struct P2PArgs {
   int scatter_only;                // reduce-scatter mode: keep the sum of my slice locally, send nothing back
   float* sq_out;                   // local, optional: += sum of squares of the reduced values this rank produced
   float* mc;                       // multicast (NVLS) address of the arena, or null
+  int tune;                        // bits 0-3: requests in flight per thread (U), bit 4: block-contiguous iteration
 };
 
 __device__ __forceinline__ void st_release_sys(unsigned int* p, unsigned int v) {
@@ -51,7 +52,7 @@ __device__ __forceinline__ unsigned int ld_acquire_sys(const unsigned int* p) {
 }
 __device__ __forceinline__ float4 ld_peer_f4(const float* p) {
   float4 v;
-  asm volatile("ld.volatile.global.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(p) : "memory");
+  asm volatile("ld.relaxed.sys.global.L1::no_allocate.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(p) : "memory");
   return v;
 }
 __device__ __forceinline__ void st_peer_f4(float* p, const float4& v) {
@@ -116,6 +117,68 @@ __device__ __forceinline__ int flag_index(int phase, int bucket, int src, int ma
   return (phase * max_buckets + bucket) * kMaxRanks + src;
 }
 
+// ---- slice loops of the two-shot / reduce-scatter paths (U independent 16-byte requests in flight per thread) ----
+template <int U>
+__device__ __forceinline__ float nvls_slice(const P2PArgs& a, long long base, long long step, long long limit) {
+  float sq = 0.f;
+  for (long long i0 = base; i0 < limit; i0 += U * step) {
+    float4 v[U];
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const long long i = i0 + u * step;
+      if (i < limit) v[u] = multimem_ld_reduce_f4(a.mc + a.start + (i << 2));
+    }
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const long long i = i0 + u * step;
+      if (i < limit) {
+        if (a.scatter_only) *reinterpret_cast<float4*>(a.data[a.rank] + a.start + (i << 2)) = v[u];
+        else multimem_st_f4(a.mc + a.start + (i << 2), v[u]);
+        sq += v[u].x * v[u].x + v[u].y * v[u].y + v[u].z * v[u].z + v[u].w * v[u].w;
+      }
+    }
+  }
+  return sq;
+}
+
+template <int U>
+__device__ __forceinline__ float peer_slice(const P2PArgs& a, long long base, long long step, long long limit) {
+  float sq = 0.f;
+  for (long long i0 = base; i0 < limit; i0 += U * step) {
+    float4 v[U][kMaxRanks];                   // U x W float4 live: U = 4 would spill at W = 8
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const long long i = i0 + u * step;
+      if (i < limit) {
+        const long long e = a.start + (i << 2);
+#pragma unroll
+        for (int p = 0; p < kMaxRanks; ++p)
+          if (p < a.world) v[u][p] = (p == a.rank) ? *reinterpret_cast<const float4*>(a.data[p] + e) : ld_peer_f4(a.data[p] + e);
+      }
+    }
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const long long i = i0 + u * step;
+      if (i < limit) {
+        const long long e = a.start + (i << 2);
+        float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+        for (int p = 0; p < kMaxRanks; ++p)      // fixed rank order -> identical bits on every rank
+          if (p < a.world) { acc.x += v[u][p].x; acc.y += v[u][p].y; acc.z += v[u][p].z; acc.w += v[u][p].w; }
+        if (a.scatter_only) {
+          *reinterpret_cast<float4*>(a.data[a.rank] + e) = acc;
+        } else {
+#pragma unroll
+          for (int p = 0; p < kMaxRanks; ++p)
+            if (p < a.world) st_peer_f4(a.data[p] + e, acc);
+        }
+        sq += acc.x * acc.x + acc.y * acc.y + acc.z * acc.z + acc.w * acc.w;
+      }
+    }
+  }
+  return sq;
+}
+
 __global__ void __launch_bounds__(kP2PThreads)
 p2p_allreduce_kernel(const P2PArgs a) {
   const int t = threadIdx.x;
@@ -171,67 +234,26 @@ p2p_allreduce_kernel(const P2PArgs a) {
   }
 
   // ---- two-shot: reduce my slice over all ranks, push the result to every rank -----------------------------
+  // Iteration space: interleaved (consecutive warps of the whole grid touch consecutive 512 B; a thread's U requests
+  // are a grid apart) or block-contiguous (each block streams its own chunk; a thread's U requests are a block apart).
   float sq = 0.f;
-  if (a.mc != nullptr) {
-    // NVLS: one multimem.ld_reduce pulls the 8-way sum out of the switch, one multimem.st replicates it to all
-    // ranks: S/W in + S/W out per GPU instead of (W-1)/W * S each way.
+  {
     const long long per = ((n4 + a.world - 1) / a.world);
     const long long lo = per * a.rank, hi = (lo + per < n4) ? lo + per : n4;
-    const long long stride = (long long)gridDim.x * blockDim.x;
-    constexpr int U = 4;
-    for (long long i0 = lo + (long long)blockIdx.x * blockDim.x + t; i0 < hi; i0 += U * stride) {
-      float4 v[U];
-#pragma unroll
-      for (int u = 0; u < U; ++u) {
-        const long long i = i0 + u * stride;
-        if (i < hi) v[u] = multimem_ld_reduce_f4(a.mc + a.start + (i << 2));
-      }
-#pragma unroll
-      for (int u = 0; u < U; ++u) {
-        const long long i = i0 + u * stride;
-        if (i < hi) {
-          if (a.scatter_only) *reinterpret_cast<float4*>(a.data[a.rank] + a.start + (i << 2)) = v[u];
-          else multimem_st_f4(a.mc + a.start + (i << 2), v[u]);
-          sq += v[u].x * v[u].x + v[u].y * v[u].y + v[u].z * v[u].z + v[u].w * v[u].w;
-        }
-      }
+    long long base, step, limit;
+    if (a.tune & 16) {
+      const long long chunk = ((hi - lo + gridDim.x - 1) / gridDim.x + 3) & ~3ll;
+      const long long c_lo = lo + (long long)blockIdx.x * chunk;
+      base = c_lo + t; step = blockDim.x; limit = (c_lo + chunk < hi) ? c_lo + chunk : hi;
+    } else {
+      base = lo + (long long)blockIdx.x * blockDim.x + t; step = (long long)gridDim.x * blockDim.x; limit = hi;
     }
-  } else {
-    const long long per = ((n4 + a.world - 1) / a.world);
-    const long long lo = per * a.rank, hi = (lo + per < n4) ? lo + per : n4;
-    const long long stride = (long long)gridDim.x * blockDim.x;
-    constexpr int U = 2;                      // independent 16-byte requests per peer in flight per thread (U x W float4 live: 4 would spill)
-    for (long long i0 = lo + (long long)blockIdx.x * blockDim.x + t; i0 < hi; i0 += U * stride) {
-      float4 v[U][kMaxRanks];
-#pragma unroll
-      for (int u = 0; u < U; ++u) {
-        const long long i = i0 + u * stride;
-        if (i < hi) {
-          const long long e = a.start + (i << 2);
-#pragma unroll
-          for (int p = 0; p < kMaxRanks; ++p)
-            if (p < a.world) v[u][p] = (p == a.rank) ? *reinterpret_cast<const float4*>(a.data[p] + e) : ld_peer_f4(a.data[p] + e);
-        }
-      }
-#pragma unroll
-      for (int u = 0; u < U; ++u) {
-        const long long i = i0 + u * stride;
-        if (i < hi) {
-          const long long e = a.start + (i << 2);
-          float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
-#pragma unroll
-          for (int p = 0; p < kMaxRanks; ++p)      // fixed rank order -> identical bits on every rank
-            if (p < a.world) { acc.x += v[u][p].x; acc.y += v[u][p].y; acc.z += v[u][p].z; acc.w += v[u][p].w; }
-          if (a.scatter_only) {
-            *reinterpret_cast<float4*>(a.data[a.rank] + e) = acc;
-          } else {
-#pragma unroll
-            for (int p = 0; p < kMaxRanks; ++p)
-              if (p < a.world) st_peer_f4(a.data[p] + e, acc);
-          }
-          sq += acc.x * acc.x + acc.y * acc.y + acc.z * acc.z + acc.w * acc.w;
-        }
-      }
+    const int u = a.tune & 15;
+    if (a.mc != nullptr) {
+      // NVLS: one multimem.ld_reduce pulls the W-way sum out of the switch, one multimem.st replicates it to all ranks
+      sq = u >= 8 ? nvls_slice<8>(a, base, step, limit) : (u >= 4 ? nvls_slice<4>(a, base, step, limit) : nvls_slice<2>(a, base, step, limit));
+    } else {
+      sq = u >= 2 ? peer_slice<2>(a, base, step, limit) : peer_slice<1>(a, base, step, limit);
     }
   }
   if (a.sq_out != nullptr) {
@@ -279,6 +301,7 @@ struct ShardedAdamArgs {
   unsigned int* counter;
   int rank, world, bucket, max_buckets;
   unsigned int* epoch_dev;
+  const float* gate;                 // optional device flag: 0 -> nothing to apply (only the flag round runs)
   AdamArgsDev adam;
 };
 
@@ -310,7 +333,10 @@ p2p_sharded_adam_kernel(const ShardedAdamArgs a) {
   const bool bf16_mode = a.p16[a.rank] != nullptr;
   float* const p_local = a.param[a.rank];
 
-  for (int b = 0; b < a.n_buckets; ++b) {
+  // a deferred update that was already flushed leaves the gate at 0: the launch still takes part in the flag round
+  // (every rank launches the same sequence of kernels) but touches no data
+  const int nb = (a.gate == nullptr || *a.gate != 0.f) ? a.n_buckets : 0;
+  for (int b = 0; b < nb; ++b) {
     const long long start = a.ranges[2 * b], n4 = a.ranges[2 * b + 1] >> 2;
     const long long per = (n4 + a.world - 1) / a.world;
     const long long lo = per * a.rank, hi = (lo + per < n4) ? lo + per : n4;
@@ -419,7 +445,8 @@ extern "C" int b200_ipc_close(void* base) {
 
 static int launch_reduce(void* const* data_ptrs, void* const* flag_ptrs, void* counter, int rank, int world,
                          long long start, long long n, int bucket, int max_buckets, void* epoch_dev, int one_shot,
-                         int scatter_only, int blocks, float* sq_out, void* multicast_base, void* stream, const char* who) {
+                         int scatter_only, int blocks, float* sq_out, void* multicast_base, void* stream, const char* who,
+                         int tune = 0) {
   if (!data_ptrs || !flag_ptrs || !counter || !epoch_dev) return fail(B200_ERR_ARG, "%s: null pointer", who);
   if (world < 2 || world > kMaxRanks || rank < 0 || rank >= world) return fail(B200_ERR_ARG, "%s: bad rank/world %d/%d", who, rank, world);
   if ((start & 3) || (n & 3)) return fail(B200_ERR_ARG, "%s: range must be a multiple of 4 elements", who);
@@ -434,6 +461,8 @@ static int launch_reduce(void* const* data_ptrs, void* const* flag_ptrs, void* c
   a.epoch_dev = static_cast<unsigned int*>(epoch_dev); a.one_shot = one_shot; a.scatter_only = scatter_only;
   a.sq_out = sq_out;
   a.mc = one_shot ? nullptr : static_cast<float*>(multicast_base);
+  if ((tune & 15) == 0) tune |= a.mc ? 4 : 2;
+  a.tune = tune;
   if (blocks <= 0) blocks = 32;
   // blocks >= 1000 encodes a narrower CTA: value = threads * 1000 + blocks (threads a multiple of 32, <= 512).
   // Many narrow CTAs spread the copy warps over every SM instead of loading a few SMs heavily, which matters
@@ -461,21 +490,24 @@ static int launch_reduce(void* const* data_ptrs, void* const* flag_ptrs, void* c
 extern "C" int b200_p2p_allreduce(void* const* data_ptrs, void* const* flag_ptrs, void* counter, int rank, int world,
                                   long long start, long long n, int bucket, int max_buckets, void* epoch_dev,
                                   int one_shot, int blocks, float* sq_out, void* multicast_base, void* stream) {
+  const char* e = getenv("B200_P2P_TUNE");
   return launch_reduce(data_ptrs, flag_ptrs, counter, rank, world, start, n, bucket, max_buckets, epoch_dev, one_shot, 0,
-                       blocks, sq_out, multicast_base, stream, "p2p_allreduce");
+                       blocks, sq_out, multicast_base, stream, "p2p_allreduce", e ? atoi(e) : 0);
 }
 
 extern "C" int b200_p2p_reduce_scatter(void* const* data_ptrs, void* const* flag_ptrs, void* counter, int rank, int world,
                                        long long start, long long n, int bucket, int max_buckets, void* epoch_dev,
                                        int blocks, float* sq_out, void* multicast_base, void* stream) {
+  // B200_P2P_TUNE = U + 16 * contiguous (see P2PArgs::tune), read per launch so that the probe tool can sweep it
+  const char* e = getenv("B200_P2P_TUNE");
   return launch_reduce(data_ptrs, flag_ptrs, counter, rank, world, start, n, bucket, max_buckets, epoch_dev, 0, 1,
-                       blocks, sq_out, multicast_base, stream, "p2p_reduce_scatter");
+                       blocks, sq_out, multicast_base, stream, "p2p_reduce_scatter", e ? atoi(e) : 0);
 }
 
 extern "C" int b200_p2p_sharded_adam(void* const* param_ptrs, void* param_mc, void* const* bf16_ptrs, void* bf16_mc,
                                      float* grad, float* m, float* v, const long long* ranges, int n_buckets, long long total,
                                      void* const* flag_ptrs, void* counter, int rank, int world, int bucket, int max_buckets,
-                                     void* epoch_dev, const b200_adam_args* args, int blocks, void* stream) {
+                                     void* epoch_dev, const b200_adam_args* args, int blocks, const float* gate, void* stream) {
   if (!param_ptrs || !grad || !m || !v || !ranges || !flag_ptrs || !counter || !epoch_dev || !args)
     return fail(B200_ERR_ARG, "p2p_sharded_adam: null pointer");
   if (world < 2 || world > kMaxRanks || rank < 0 || rank >= world) return fail(B200_ERR_ARG, "p2p_sharded_adam: bad rank/world %d/%d", rank, world);
@@ -497,6 +529,7 @@ extern "C" int b200_p2p_sharded_adam(void* const* param_ptrs, void* param_mc, vo
   a.counter = static_cast<unsigned int*>(counter);
   a.rank = rank; a.world = world; a.bucket = bucket; a.max_buckets = max_buckets;
   a.epoch_dev = static_cast<unsigned int*>(epoch_dev);
+  a.gate = gate;
   fill_adam_args(args, a.adam);
   if (blocks <= 0) blocks = num_sms() * 8;
   p2p_sharded_adam_kernel<<<blocks, 256, 0, (cudaStream_t)stream>>>(a);

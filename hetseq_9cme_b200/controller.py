@@ -109,6 +109,8 @@ class Controller:
         self._graph_steps_total = 0
         self._graph_pool = None
         self._g_hyper = None
+        self._defer_update = False
+        self._pending_hyper = None
         self.init_meters(args)
 
     # ------------------------------------------------------------------------------------------------
@@ -212,6 +214,7 @@ class Controller:
         self._optimizer.attach_arena(arena)
         self._lr_scheduler = lr_sched.build_lr_scheduler(self.args, self._optimizer)
         self._lr_scheduler.step_update(0)
+        self._init_deferral()
 
     # ---- checkpoints ---------------------------------------------------------------------------------
     def _meters_state(self):
@@ -221,6 +224,7 @@ class Controller:
         """Collective (every rank): with the sharded optimizer step each rank keeps only its slices of the Adam
         moments (and, in bf16 mode, of the fp32 masters) current — gather them so that the master rank can write the
         reference's checkpoint schema unchanged."""
+        self.flush_pending_update()
         self.flush_stats()
         red = self._reducer
         if red is not None and getattr(red, "sharded", False) and self._optimizer is not None:
@@ -429,7 +433,26 @@ class Controller:
         else:
             kernels.sumsq(arena.grad, ws.norm_sq, ws=ws)
             norm_sq = ws.norm_sq
-        kw = dict(grad_scale_mult=mult, max_norm=float(getattr(self.args, "clip_norm", 0.0)), norm_sq=norm_sq,
+        max_norm = float(getattr(self.args, "clip_norm", 0.0))
+        if self._defer_update:
+            # The sharded update ends with the parameter broadcast — NVLink-bound and, placed here, fully exposed.
+            # Park what it needs instead ({sum g^2, sample size, valid}, this step's schedule values) and let the NEXT
+            # step issue it bucket by bucket next to its forward pass (_apply_pending_update).  gnorm / clip for the
+            # log are derived here from the same scalars.
+            pend = self._pend
+            pend[0:1].copy_(norm_sq)
+            if sample_size_dev is not None:
+                pend[1:2].copy_(sample_size_dev.float() / mult if mult != 1.0 else sample_size_dev)
+            else:
+                pend[1:2].fill_(1.0 / mult)
+            pend[2:3].fill_(1.0)
+            self._pending_hyper = list(opt.hyper_values(opt._global_step + 1))
+            scale = torch.where(pend[1:2] > 0, 1.0 / pend[1:2].clamp_min(1e-30), torch.zeros_like(pend[1:2]))
+            gnorm = pend[0:1].clamp_min(0).sqrt() * scale
+            ws.step_stats[0:1].copy_(gnorm)
+            ws.step_stats[2:3].copy_(((gnorm > max_norm) & (max_norm > 0)).float())
+            return ws.step_stats
+        kw = dict(grad_scale_mult=mult, max_norm=max_norm, norm_sq=norm_sq,
                   sample_size=sample_size_dev, stats_out=ws.step_stats, hyper_dev=hyper_dev, advance=advance)
         with self._range("update"):
             if getattr(reducer, "sharded", False):
@@ -438,9 +461,67 @@ class Controller:
                 opt.fused_step(zero_grad=True, **kw)
         return ws.step_stats
 
+    # ---- deferred (pipelined) sharded update ---------------------------------------------------------------------
+    def _init_deferral(self):
+        red = self._reducer
+        self._defer_update = bool(self.cuda and getattr(red, "sharded", False) and not os.environ.get("B200_NO_DEFER")
+                                  and not getattr(self.args, "no_pipelined_update", False))
+        self._pending_hyper = None
+        if self._defer_update:
+            self._pend = torch.zeros(4, dtype=torch.float32, device=self.device)          # sum g^2, sample size, valid
+            self._pend_hyper_dev = torch.zeros(4, dtype=torch.float32, device=self.device)
+            self._pend_hyper_host = [torch.zeros(4, dtype=torch.float32).pin_memory() for _ in range(4)]
+            self._pend_hyper_i = 0
+
+    def _stage_pending_hyper(self):
+        """Schedule values of the parked update -> device (async copy from a small pinned ring; before the launch /
+        replay that applies it)."""
+        if not self._defer_update:
+            return
+        h = self._pend_hyper_host[self._pend_hyper_i % 4]
+        self._pend_hyper_i += 1
+        vals = self._pending_hyper or [0.0, 0.0, 1.0, 0.0]
+        for i, v in enumerate(vals):
+            h[i] = v
+        self._pend_hyper_dev.copy_(h, non_blocking=True)
+
+    def _apply_pending_update(self, pipelined=True):
+        """Issue the parked update (every step, also when nothing is parked: the kernels carry a flag round that all
+        ranks must run; the device-side gate makes them skip the data).  Pipelined: on the reducer's side stream, the
+        forward pass waits per bucket.  Otherwise on the training stream (flush)."""
+        if not self._defer_update:
+            return
+        opt, red = self._optimizer.optimizer, self._reducer
+        with self._range("update"):
+            opt.sharded_step(red, grad_scale_mult=1.0, max_norm=float(getattr(self.args, "clip_norm", 0.0)),
+                             norm_sq=self._pend[0:1], sample_size=self._pend[1:2], stats_out=None,
+                             hyper_dev=self._pend_hyper_dev, advance=False, gate=self._pend[2:3], pipelined=pipelined)
+        if not pipelined:
+            self._pend[2:3].zero_()         # same stream as the launch: ordered after it
+        elif not (hasattr(self._model, "bind_arena") and not getattr(self._model, "force_torch_path", False)):
+            red.need_all()                  # models on plain PyTorch ops do not announce what they read
+
+    def _note_update_applied(self):
+        """Host bookkeeping after the launch / replay that applied a parked update."""
+        if self._defer_update and self._pending_hyper is not None:
+            self._optimizer.optimizer._global_step += 1
+            self._pending_hyper = None
+
+    def flush_pending_update(self):
+        """Apply a parked update now (collective: every rank calls it at the same point) — before anything reads the
+        parameters outside a training step: validation, checkpoints, the end of training."""
+        if not getattr(self, "_defer_update", False) or self._pending_hyper is None:
+            return
+        self._stage_pending_hyper()
+        self._apply_pending_update(pipelined=False)
+        self._note_update_applied()
+
     def _eager_step_cuda(self, samples, dummy_batch):
         dev = self.device
         tail = self._arena.tail
+        self._stage_pending_hyper()
+        self._apply_pending_update()
+        self._note_update_applied()
         tail.zero_()
         stat_sum = torch.zeros(self._mailbox.FIELDS, dtype=torch.float64, device=dev)
 
@@ -451,6 +532,8 @@ class Controller:
         if dummy_batch:
             with self._range("reduce_wait"):
                 self._reducer.finish()
+            if self._defer_update:
+                self._pend[2:3].zero_()     # the parked update was applied above and this step parks none
             return None
 
         # ---- statistics: global sums ride the tail (one peer reduction, no NCCL call, no host sync) --------------
@@ -565,6 +648,8 @@ class Controller:
             return False
         if not hasattr(self.task, "_sample_size"):
             return False
+        if type(self._reducer).__name__ == "TorchReducer":
+            return False       # NCCL / gloo collectives stay outside graphs (decided by flags: the same on every rank)
         sig = self._sig(samples)
         if sig in self._graph_cache:
             return True
@@ -585,6 +670,7 @@ class Controller:
         from .ops import kernels
         arena, reducer = self._arena, self._reducer
         tail = arena.tail
+        self._apply_pending_update()          # last step's parked update, next to this step's forward pass
         tail.zero_()
         n = len(st["samples"])
         for i in range(n):
@@ -595,7 +681,6 @@ class Controller:
             lf = loss.detach().reshape(1).float()
             tail[0:1] += lf
             tail[1:2] += lf
-            self._note_mlm_overflow()
             if i == n - 1:
                 st["last_loss"].copy_(lf)
         tail[2:5] += st["const"]
@@ -610,9 +695,6 @@ class Controller:
             self._g_out[0:2] = st["last_loss"].double().expand(2)
             self._g_out[2:5] = st["const_last"].double()
         self._g_out[5:7] = step_stats[0:3:2].double()
-        if getattr(self, "_mlm_over", None) is not None:
-            self._g_out[7:8] = self._mlm_over
-            self._mlm_over.zero_()
 
     def _graph_capture(self, samples):
         dev = self.device
@@ -645,7 +727,8 @@ class Controller:
         st["const"] = torch.tensor([ss_sum, ns_sum, ntok_sum], dtype=torch.float32, device=dev)
         st["const_last"] = torch.tensor([ss, ns, nt], dtype=torch.float32, device=dev)
         st["last_loss"] = torch.zeros(1, dtype=torch.float32, device=dev)
-        self._stage_hyper()
+        if not self._defer_update:
+            self._stage_hyper()
         torch.cuda.synchronize()
         # capture on a side stream, as torch requires; state changes made while capturing are real work that is
         # NOT executed (capture only records), so the first real execution is the first replay below
@@ -690,12 +773,17 @@ class Controller:
             else:
                 for dst, src in zip(static, sample):
                     dst.copy_(src, non_blocking=True)
-        self._stage_hyper()
+        if self._defer_update:
+            self._stage_pending_hyper()
+        else:
+            self._stage_hyper()
         st["graph"].replay()
         from .ops import native
         native.add_launch_count(st["launches"])
-        opt = self.optimizer.optimizer
-        opt._global_step += 1
+        if self._defer_update:
+            self._note_update_applied()
+        else:
+            self.optimizer.optimizer._global_step += 1
         return self._finish_step(self._g_out)
 
     def watchdog_report(self) -> Optional[str]:
@@ -745,6 +833,7 @@ class Controller:
     def valid_step(self, sample, raise_oom=False):
         """Forward only; returns ``{'loss', 'sample_size', 'nsentences', 'ntokens'}`` summed over ranks."""
         model = self.model
+        self.flush_pending_update()
         model.eval()
         sample = self._prepare_sample(sample)
         ignore = sample is None

@@ -29,6 +29,9 @@ class GradSink:
     def ready(self, params) -> None:  # pragma: no cover - default is a no-op
         pass
 
+    def need(self, params) -> None:  # pragma: no cover - default is a no-op
+        """Forward is about to read these parameters (a pipelined optimizer step may still be writing later ones)."""
+
 
 _NULL_SINK = GradSink()
 
@@ -63,6 +66,7 @@ class EmbeddingsFn(torch.autograd.Function):
         ids = input_ids.reshape(-1).contiguous()
         tts = token_type_ids.reshape(-1).contiguous() if token_type_ids is not None else None
         W, P, T = emb.word_embeddings.weight, emb.position_embeddings.weight, emb.token_type_embeddings.weight
+        nctx.sink.need([W, P, T, emb.LayerNorm.weight, emb.LayerNorm.bias])
         s = K.embed_sum(ids, tts, W, P, T, L)
         p = emb.dropout.p if nctx.training else 0.0
         y, mean, rstd = K.ln_fwd(s, emb.LayerNorm.weight, emb.LayerNorm.bias, eps=emb.LayerNorm.variance_epsilon,
@@ -165,6 +169,7 @@ def _layer_forward(x, nctx, lp, attn_mask, B, L, sid, p_attn, p_hid):
     heads, dh = lp.heads, lp.dh
     Lp = _pad8(L)
     dev, dt = x.device, x.dtype
+    nctx.sink.need(lp.params)
     qkv = gemm(x, lp.Wqkv, bias=lp.bqkv)                                                    # [M, 3H]
     if _fused_attention(L, dh):
         ctxv, lse = K.attn_fwd(qkv, attn_mask, B, heads, L, 1.0 / math.sqrt(dh), p_attn, nctx.seed, sid + 1, Lp=Lp)
@@ -287,6 +292,7 @@ class PoolerFn(torch.autograd.Function):
     @staticmethod
     def forward(ctx, seq2d, nctx: NativeCtx, pooler, B: int, L: int):
         first = seq2d.view(B, L, -1)[:, 0]                       # [B, H] rows strided by L*H
+        nctx.sink.need([pooler.dense_act.weight, pooler.dense_act.bias])
         y = gemm(first, pooler.dense_act.weight, bias=pooler.dense_act.bias, act=N.ACT_TANH)
         ctx.nctx, ctx.pooler, ctx.dims = nctx, pooler, (B, L)
         ctx.save_for_backward(seq2d, y)
@@ -330,6 +336,7 @@ class PretrainLossFn(torch.autograd.Function):
         V, H = emb_w.shape
         dt, dev = seq2d.dtype, seq2d.device
         labels = mlm_labels.reshape(-1).contiguous()
+        nctx.sink.need(list(heads.parameters()) + list(model.bert.pooler.parameters()))
 
         idx, lab, cnt = K.compact_rows(labels, cap, ignore=-1)
         hsel = K.gather_rows(seq2d, idx)                                                   # [cap, H]
@@ -422,6 +429,7 @@ class TokenClsLossFn(torch.autograd.Function):
     def forward(ctx, seq2d, nctx: NativeCtx, model, labels, attention_mask, sid: int):
         p = model.dropout.p if nctx.training else 0.0
         w, b = model.classifier.weight, model.classifier.bias
+        nctx.sink.need([w, b])
         x = K.dropout(seq2d.contiguous(), p, nctx.seed, sid) if p > 0 else seq2d.contiguous()
         logits = K.head_fwd(x, w, b)                                                         # fp32 [M, C]
         lab = labels.reshape(-1).contiguous()

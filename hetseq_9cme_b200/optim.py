@@ -173,7 +173,7 @@ class Adam(_ArenaMixin, torch.optim.Optimizer):
             self.mark_step()
 
     def sharded_step(self, reducer, *, grad_scale_mult: float = 1.0, max_norm: float = 0.0, norm_sq=None, sample_size=None,
-                     stats_out=None, hyper_dev=None, advance: bool = True):
+                     stats_out=None, hyper_dev=None, advance: bool = True, gate=None, pipelined: bool = False):
         """The same update restricted to the arena slices this rank owns, with the new parameters written into every
         rank by the kernel itself (``parallel/p2p.py``); moments of slices owned elsewhere are not maintained here —
         ``reducer.gather_sharded`` makes them whole before a checkpoint."""
@@ -185,7 +185,8 @@ class Adam(_ArenaMixin, torch.optim.Optimizer):
                                       weight_decay=g["weight_decay"], step=max(self._global_step, 1),
                                       grad_scale_mult=grad_scale_mult, max_norm=max_norm, norm_sq=norm_sq,
                                       sample_size=sample_size, stats_out=stats_out, zero_grad=True, hyper_dev=hyper_dev)
-        reducer.sharded_adam(args, self._flat_state["exp_avg"], self._flat_state["exp_avg_sq"])
+        launch = reducer.sharded_adam_pipelined if pipelined else reducer.sharded_adam
+        launch(args, self._flat_state["exp_avg"], self._flat_state["exp_avg_sq"], gate=gate)
         if advance:
             self.mark_step()
 

@@ -204,6 +204,9 @@ _ENGINE = [
                                        help="peer-to-peer reducer: all-reduce the gradients and run the optimizer "
                                             "replicated on every rank instead of reduce-scatter + owned-slice update + "
                                             "parameter broadcast")),
+    (("--no-pipelined-update",), dict(action="store_true",
+                                      help="sharded optimizer step: run it (and its parameter broadcast) at the end of the step "
+                                           "instead of parking it and issuing it per bucket under the next forward pass")),
     (("--checkpoint-activations",), dict(action="store_true", help="recompute encoder activations in backward")),
     (("--pad-to-multiple-of",), dict(type=int, default=0, metavar="N",
                                      help="NER / EL collators: pad the batch width up to a multiple of N (0: longest "

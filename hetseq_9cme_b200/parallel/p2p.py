@@ -191,7 +191,7 @@ def _declare(lib):
     lib.b200_p2p_allreduce.restype = I
     lib.b200_p2p_reduce_scatter.argtypes = [PP, PP, P, I, I, LL, LL, I, I, P, I, P, P, P]
     lib.b200_p2p_reduce_scatter.restype = I
-    lib.b200_p2p_sharded_adam.argtypes = [PP, P, PP, P, P, P, P, P, I, LL, PP, P, I, I, I, I, P, P, I, P]
+    lib.b200_p2p_sharded_adam.argtypes = [PP, P, PP, P, P, P, P, P, I, LL, PP, P, I, I, I, I, P, P, I, P, P]
     lib.b200_p2p_sharded_adam.restype = I
     lib.b200_p2p_set_watchdog.argtypes = [D, P]
     lib.b200_p2p_set_watchdog.restype = I
@@ -224,7 +224,7 @@ class P2PReducer(BaseReducer):
             raise RuntimeError("P2PReducer needs CUDA")
         if world_size > MAX_RANKS:
             raise RuntimeError("P2PReducer supports at most %d ranks (one NVSwitch domain)" % MAX_RANKS)
-        if len(arena.buckets) + 2 > MAX_BUCKETS:
+        if 2 * len(arena.buckets) + 2 > MAX_BUCKETS:
             raise RuntimeError("too many buckets for the flag array")
         self.lib = native.cuda_lib()
         _declare(self.lib)
@@ -234,6 +234,12 @@ class P2PReducer(BaseReducer):
         # CTA width of the launches that overlap backward (see b200_p2p_allreduce: threads * 1000 + blocks)
         self.threads = int(os.environ.get("B200_P2P_THREADS", 512))
         self.no_overlap = bool(os.environ.get("B200_P2P_NO_OVERLAP"))
+        # data paths of the sharded mode: NVLS (multimem) or plain peer loads / stores.  In-switch reduction keeps the
+        # inbound traffic of a reduce-scatter at S/W, a multicast store keeps the outbound traffic of the broadcast at
+        # S/W — but both loop this rank's own share through the switch as well; B200_RS_PEER / B200_BCAST_PEER select
+        # the peer forms (measured per rank count in profiles/README.md)
+        self.rs_peer = bool(os.environ.get("B200_RS_PEER"))
+        self.bcast_peer = bool(os.environ.get("B200_BCAST_PEER"))
         self._dry = bool(os.environ.get("B200_P2P_DRY"))
         # B200_P2P_DEBUG=1: every bucket is also reduced with torch.distributed (NCCL) from a copy taken right before
         # the launch, and compared after the step; the per-bucket epoch counters are checked against the host's count.
@@ -404,6 +410,8 @@ class P2PReducer(BaseReducer):
         grid = self.tail_blocks if self._after_backward else self._overlap_grid()
         mc = self.mc_base if (self.mc_base and n * 4 >= NVLS_MIN_BYTES) else 0
         if self.sharded:
+            if self.rs_peer:
+                mc = 0
             native.check(self.lib.b200_p2p_reduce_scatter(self.data_ptrs, self.flag_ptrs, self.counter.data_ptr(), self.rank,
                                                           self.world_size, s, n, bi, MAX_BUCKETS, self.epochs.data_ptr(), grid,
                                                           self.sq_ptr, mc, self._side.cuda_stream), "b200_p2p_reduce_scatter")
@@ -470,18 +478,58 @@ class P2PReducer(BaseReducer):
         hi = min(lo + per, n4)
         return s + 4 * lo, s + 4 * hi
 
-    def sharded_adam(self, adam_args, m: torch.Tensor, v: torch.Tensor):
-        """Scale / clip / Adam on the slices this rank owns + parameter broadcast + zero_grad (training stream)."""
+    def _sharded_launch(self, adam_args, m, v, first: int, count: int, slot: int, gate, stream):
         a = self.arena
         bf16 = a.work is not None
         native.check(self.lib.b200_p2p_sharded_adam(
             self.param_ptrs if self.param_ptrs is not None else _ptr_array([a.master.data_ptr() if r == self.rank else 0 for r in range(self.world_size)]),
-            self.param_mc if not bf16 else None,
-            self.work_ptrs if bf16 else None, (self.work_mc or None) if bf16 else None,
-            a.grad.data_ptr(), m.data_ptr(), v.data_ptr(), self.ranges.data_ptr(), len(a.buckets), a.numel,
-            self.flag_ptrs, self.counter.data_ptr(), self.rank, self.world_size, len(a.buckets) + 1, MAX_BUCKETS,
+            (self.param_mc or None) if not (bf16 or self.bcast_peer) else None,
+            self.work_ptrs if bf16 else None, (self.work_mc or None) if (bf16 and not self.bcast_peer) else None,
+            a.grad.data_ptr(), m.data_ptr(), v.data_ptr(), self.ranges.data_ptr() + 16 * first, count, a.numel,
+            self.flag_ptrs, self.counter.data_ptr(), self.rank, self.world_size, slot, MAX_BUCKETS,
             self.epochs.data_ptr(), ctypes.byref(adam_args), int(os.environ.get("B200_SHARDED_ADAM_BLOCKS", "0")),
-            torch.cuda.current_stream().cuda_stream), "b200_p2p_sharded_adam")
+            gate.data_ptr() if gate is not None else None, stream), "b200_p2p_sharded_adam")
+
+    def sharded_adam(self, adam_args, m: torch.Tensor, v: torch.Tensor, gate=None):
+        """Scale / clip / Adam on the slices this rank owns + parameter broadcast + zero_grad, one kernel on the
+        training stream."""
+        self._sharded_launch(adam_args, m, v, 0, len(self.arena.buckets), len(self.arena.buckets) + 1, gate,
+                             torch.cuda.current_stream().cuda_stream)
+
+    def sharded_adam_pipelined(self, adam_args, m: torch.Tensor, v: torch.Tensor, gate=None):
+        """The same update issued bucket by bucket on the side stream, first layers first: the training stream does not
+        wait here — the forward pass that follows calls ``need(params)`` per block and waits only for the bucket that
+        holds those parameters, so the parameter broadcast of the later layers runs under the first layers' compute."""
+        nb = len(self.arena.buckets)
+        ev = torch.cuda.Event()
+        ev.record(torch.cuda.current_stream())
+        self._side.wait_event(ev)
+        self._param_events = {}
+        for bi in range(nb - 1, -1, -1):             # buckets are numbered from the END of the arena: last = embeddings
+            self._sharded_launch(adam_args, m, v, bi, 1, nb + 1 + bi, gate, self._side.cuda_stream)
+            e = torch.cuda.Event()
+            e.record(self._side)
+            self._param_events[bi] = e
+
+    def need(self, params) -> None:
+        """Forward is about to read these parameters: wait for the pipelined update of their buckets (once each)."""
+        evs = getattr(self, "_param_events", None)
+        if not evs:
+            return
+        cur = torch.cuda.current_stream()
+        for p in params:
+            bi = self.arena.bucket_of.get(id(p))
+            e = evs.pop(bi, None) if bi is not None else None
+            if e is not None:
+                cur.wait_event(e)
+
+    def need_all(self) -> None:
+        evs = getattr(self, "_param_events", None)
+        if evs:
+            cur = torch.cuda.current_stream()
+            for e in evs.values():
+                cur.wait_event(e)
+            evs.clear()
 
     def gather_sharded(self, flats) -> None:
         """Make flat fp32 tensors whose slices are only current on their owners (optimizer moments; the fp32 masters in

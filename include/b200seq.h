@@ -293,11 +293,15 @@ int b200_p2p_reduce_scatter(void* const* data_ptrs, void* const* flag_ptrs, void
  * null, otherwise the fp32 master stays local (only the owner's slice is kept current) and the bf16 working copy
  * is what travels (bf16_ptrs / bf16_mc).  It also zeroes the whole local gradient arena [0, total).  A flag round
  * (slot `bucket`) ends the kernel: when it retires every peer's writes into this rank's parameters have landed.
+ * The update may be issued bucket by bucket (ranges + 2*b, n_buckets = 1, a flag slot per bucket) on a side stream
+ * so that the next forward pass starts as soon as the first layers' parameters are in.
  * Scalars as in b200_adam_flat (a->norm_sq / sample_size / hyper_dev / stats_out). */
 int b200_p2p_sharded_adam(void* const* param_ptrs, void* param_mc, void* const* bf16_ptrs, void* bf16_mc,
                           float* grad, float* m, float* v, const long long* ranges, int n_buckets, long long total,
                           void* const* flag_ptrs, void* counter, int rank, int world, int bucket, int max_buckets,
-                          void* epoch_dev, const b200_adam_args* a, int blocks, void* stream);
+                          void* epoch_dev, const b200_adam_args* a, int blocks,
+                          const float* gate /* optional device float: 0 skips the update, the flag round still runs */,
+                          void* stream);
 
 /* How long a kernel waits for a peer's flag before it gives up (seconds; default 600), and an optional word of
  * mapped pinned host memory that then receives (0x80000000 | slot << 8 | missing rank).  A tripped watchdog does

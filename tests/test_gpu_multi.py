@@ -72,9 +72,16 @@ def test_bf16_sharded_masters_and_checkpoint(tmp_path):
 
 
 @needs2
-def test_nccl_reducer_inside_the_graph(tmp_path):
-    """--comm torch: the NCCL all-reduces are captured with the step (like-for-like baseline of the p2p path)."""
-    _ok(_torchrun(2, ["tools/dp_debug_run.py", str(tmp_path), "--mode", "torch", "--graph", "--compare-single"]), "DP DEBUG RUN PASS")
+def test_nccl_reducer_path(tmp_path):
+    """--comm torch: NCCL all-reduces per bucket, replicated optimizer (the portable baseline of the p2p path)."""
+    _ok(_torchrun(2, ["tools/dp_debug_run.py", str(tmp_path), "--mode", "torch", "--compare-single"]), "DP DEBUG RUN PASS")
+
+
+@needs2
+def test_pipelined_update_off_matches(tmp_path):
+    """B200_NO_DEFER=1: the sharded update at the end of the step instead of under the next forward pass."""
+    _ok(_torchrun(2, ["tools/dp_debug_run.py", str(tmp_path), "--mode", "sharded", "--graph", "--compare-single"],
+                  env=dict(SMALL_BUCKETS, B200_NO_DEFER="1")), "DP DEBUG RUN PASS")
 
 
 @needs2

@@ -44,6 +44,7 @@ def build(out, a, world, rank, local, update_freq, graph, comm, extra=()):
     else:
         argv.append("--no-cuda-graph")
     args = options.parse_training_args(argv)
+    os.makedirs(args.save_dir, exist_ok=True)
     args.distributed_rank, args.device_id = (rank if world > 1 else 0), local
     torch.manual_seed(args.seed)
     task = tasks.LanguageModelingTask.setup_task(args)

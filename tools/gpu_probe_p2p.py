@@ -171,8 +171,32 @@ def main():
         t_rs, t_sh, t_rep = timed(rs_all), timed(sharded_update), timed(replicated_update)
         nb = ar.numel * 4
         if rank == 0:
-            print("BW %s: reduce-scatter %.3f ms (%.1f MB, %.1f GB/s in per GPU) | sharded Adam + broadcast %.3f ms | replicated Adam %.3f ms" % (
-                "bf16" if bf16 else "fp32", t_rs, nb / 1e6, nb / t_rs / 1e6 * (world - 1) / world, t_sh, t_rep), flush=True)
+            print("BW %s: reduce-scatter %.3f ms (%.1f MB) | sharded Adam + broadcast %.3f ms | replicated Adam %.3f ms" % (
+                "bf16" if bf16 else "fp32", t_rs, nb / 1e6, t_sh, t_rep), flush=True)
+        if not quick:
+            # sweep of the data-path knobs (all ranks change them in lock-step)
+            for peer in (False, True):
+                rs.rs_peer = peer
+                for tune in ((4, 8, 20, 24) if not peer else (1, 2, 18)):
+                    os.environ["B200_P2P_TUNE"] = str(tune)
+                    for blocks in (32, 64, 128, 296):
+                        rs.tail_blocks = blocks
+                        t = timed(rs_all, iters=6, warm=2)
+                        if rank == 0:
+                            print("SWEEP %s reduce-scatter %-5s U=%d %-11s blocks=%3d: %.3f ms" % (
+                                "bf16" if bf16 else "fp32", "peer" if peer else "nvls", tune & 15, "contiguous" if tune & 16 else "interleaved", blocks, t), flush=True)
+            os.environ.pop("B200_P2P_TUNE", None)
+            rs.rs_peer, rs.tail_blocks = False, 128
+            for peer in (False, True):
+                rs.bcast_peer = peer
+                for blocks in (148 * 2, 148 * 4, 148 * 8, 148 * 16):
+                    os.environ["B200_SHARDED_ADAM_BLOCKS"] = str(blocks)
+                    t = timed(sharded_update, iters=6, warm=2)
+                    if rank == 0:
+                        print("SWEEP %s sharded Adam + broadcast %-9s blocks=%4d: %.3f ms" % (
+                            "bf16" if bf16 else "fp32", "peer st" if peer else "multicast", blocks, t), flush=True)
+            os.environ.pop("B200_SHARDED_ADAM_BLOCKS", None)
+            rs.bcast_peer = False
     if rank == 0:
         print("P2P PROBE", "PASS" if ok else "FAIL", flush=True)
     dist.barrier()

@@ -445,8 +445,7 @@ class Controller:
                 pend[1:2].copy_(sample_size_dev.float() / mult if mult != 1.0 else sample_size_dev)
             else:
                 pend[1:2].fill_(1.0 / mult)
-            pend[2:3].fill_(1.0)
-            self._pending_hyper = list(opt.hyper_values(opt._global_step + 1))
+            pend[2:3].fill_(1.0)                  # host side of the parking: _park_host(), by the caller (not under capture)
             scale = torch.where(pend[1:2] > 0, 1.0 / pend[1:2].clamp_min(1e-30), torch.zeros_like(pend[1:2]))
             gnorm = pend[0:1].clamp_min(0).sqrt() * scale
             ws.step_stats[0:1].copy_(gnorm)
@@ -500,6 +499,13 @@ class Controller:
             self._pend[2:3].zero_()         # same stream as the launch: ordered after it
         elif not (hasattr(self._model, "bind_arena") and not getattr(self._model, "force_torch_path", False)):
             red.need_all()                  # models on plain PyTorch ops do not announce what they read
+
+    def _park_host(self):
+        """Host half of parking an update: remember the schedule values (lr, bias-corrected step size, decay) that are
+        current NOW — the kernels that apply it run after the scheduler has moved on."""
+        if self._defer_update:
+            opt = self._optimizer.optimizer
+            self._pending_hyper = list(opt.hyper_values(opt._global_step + 1))
 
     def _note_update_applied(self):
         """Host bookkeeping after the launch / replay that applied a parked update."""
@@ -559,6 +565,7 @@ class Controller:
             sample_size_dev = None
             mult = 1.0 / float(last_sample_size) if last_sample_size and last_sample_size > 0 else 1.0
         step_stats = self._device_update(tail, sample_size_dev, mult)
+        self._park_host()
         if self.fast_stat_sync:
             stat_sum[0:5] = tail[0:5].double()
         else:
@@ -781,7 +788,8 @@ class Controller:
         from .ops import native
         native.add_launch_count(st["launches"])
         if self._defer_update:
-            self._note_update_applied()
+            self._note_update_applied()        # the replay applied the previous step's update ...
+            self._park_host()                  # ... and parked this one's
         else:
             self.optimizer.optimizer._global_step += 1
         return self._finish_step(self._g_out)

@@ -238,6 +238,9 @@ class P2PReducer(BaseReducer):
         # inbound traffic of a reduce-scatter at S/W, a multicast store keeps the outbound traffic of the broadcast at
         # S/W — but both loop this rank's own share through the switch as well; B200_RS_PEER / B200_BCAST_PEER select
         # the peer forms (measured per rank count in profiles/README.md)
+        # update kernels that run NEXT TO the forward pass: few CTAs (they are NVLink-bound, and every extra resident
+        # warp takes issue slots from the persistent GEMM CTA of its SM)
+        self.pipelined_blocks = int(os.environ.get("B200_PIPELINED_BLOCKS", "148"))
         self.rs_peer = bool(os.environ.get("B200_RS_PEER"))
         self.bcast_peer = bool(os.environ.get("B200_BCAST_PEER"))
         self._dry = bool(os.environ.get("B200_P2P_DRY"))
@@ -478,7 +481,7 @@ class P2PReducer(BaseReducer):
         hi = min(lo + per, n4)
         return s + 4 * lo, s + 4 * hi
 
-    def _sharded_launch(self, adam_args, m, v, first: int, count: int, slot: int, gate, stream):
+    def _sharded_launch(self, adam_args, m, v, first: int, count: int, slot: int, gate, stream, blocks: int = 0):
         a = self.arena
         bf16 = a.work is not None
         native.check(self.lib.b200_p2p_sharded_adam(
@@ -487,7 +490,7 @@ class P2PReducer(BaseReducer):
             self.work_ptrs if bf16 else None, (self.work_mc or None) if (bf16 and not self.bcast_peer) else None,
             a.grad.data_ptr(), m.data_ptr(), v.data_ptr(), self.ranges.data_ptr() + 16 * first, count, a.numel,
             self.flag_ptrs, self.counter.data_ptr(), self.rank, self.world_size, slot, MAX_BUCKETS,
-            self.epochs.data_ptr(), ctypes.byref(adam_args), int(os.environ.get("B200_SHARDED_ADAM_BLOCKS", "0")),
+            self.epochs.data_ptr(), ctypes.byref(adam_args), int(os.environ.get("B200_SHARDED_ADAM_BLOCKS", "0")) or blocks,
             gate.data_ptr() if gate is not None else None, stream), "b200_p2p_sharded_adam")
 
     def sharded_adam(self, adam_args, m: torch.Tensor, v: torch.Tensor, gate=None):
@@ -506,7 +509,7 @@ class P2PReducer(BaseReducer):
         self._side.wait_event(ev)
         self._param_events = {}
         for bi in range(nb - 1, -1, -1):             # buckets are numbered from the END of the arena: last = embeddings
-            self._sharded_launch(adam_args, m, v, bi, 1, nb + 1 + bi, gate, self._side.cuda_stream)
+            self._sharded_launch(adam_args, m, v, bi, 1, nb + 1 + bi, gate, self._side.cuda_stream, blocks=self.pipelined_blocks)
             e = torch.cuda.Event()
             e.record(self._side)
             self._param_events[bi] = e

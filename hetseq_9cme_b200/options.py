@@ -217,6 +217,9 @@ _ENGINE = [
                                              "dense MLM labels with a kernel on the GPU; default: on when training on CUDA")),
     (("--max-predictions-per-seq",), dict(type=int, default=0, metavar="P",
                                           help="upper bound of masked positions per sequence (0: sequence length)")),
+    (("--sync-stats",), dict(action="store_true",
+                             help="wait for each step's statistics before returning from train_step (default: they reach "
+                                  "the meters one step late through a pinned mailbox, so the host never waits for the GPU)")),
     (("--profile",), dict(action="store_true", help="emit NVTX ranges per phase")),
     (("--log-jsonl",), dict(type=str, default=None, metavar="PATH", help="also append per-step stats as JSON lines")),
     (("--fault-inject",), dict(type=str, default=None, metavar="RANK:STEP", help="testing: kill RANK at STEP")),

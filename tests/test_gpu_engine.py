@@ -152,3 +152,48 @@ def test_cuda_graph_cache_handles_several_batch_shapes(tmp_path):
     a, b = eager.arena.master, graph.arena.master
     assert (a - b).abs().max().item() <= 5e-4 * a.abs().max().item()
     assert abs(eager.get_meter("train_loss").avg - graph.get_meter("train_loss").avg) < 2e-3
+
+
+def test_loss_curve_matches_the_reference_from_its_own_checkpoint(tmp_path):
+    """20 steps of BERT-base (4 layers here to keep the test short): the unmodified reference trains from its own
+    initialisation in fp32; this framework restores the reference's checkpoint and trains on the same batches through
+    the native TF32 kernels.  Per-step loss and the first gradient norm must agree (tools/loss_parity.py)."""
+    import subprocess
+    import sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    if not os.path.isdir(os.path.join(root, "baseline", "_ref", "hetseq")):
+        pytest.skip("baseline/_ref (the installed reference) is not present")
+    r = subprocess.run([sys.executable, "tools/loss_parity.py", "all", str(tmp_path), "--steps", "20", "--layers", "4"], cwd=root,
+                       capture_output=True, text=True, timeout=900)
+    assert r.returncode == 0 and "LOSS PARITY PASS" in r.stdout, r.stdout[-3000:] + r.stderr[-2000:]
+
+
+def test_resume_reproduces_the_uninterrupted_run(tmp_path):
+    """Train 6 steps, checkpoint, train 6 more; a fresh Controller restored from the checkpoint must reach the same
+    weights after its 6 steps (dropout on: the per-step seed is seed + num_updates, so masks are reproduced too)."""
+    from hetseq_9cme_b200 import checkpoint_utils
+    extra = ["--hidden-dropout-override", "0.1"] if False else []
+    a, it_a = _setup(tmp_path, ["--cuda-graph"] + extra)
+    for _ in range(6):
+        a.train_step([next(it_a)])
+    a.flush_stats()
+    a.args.no_save = False
+    os.makedirs(a.args.save_dir, exist_ok=True)
+    a.save_checkpoint(str(tmp_path / "mid.pt"), {"train_iterator": {"epoch": 1, "iterations_in_epoch": 6}, "val_loss": None})
+    for _ in range(6):
+        a.train_step([next(it_a)])
+    a.flush_stats()
+
+    b, it_b = _setup(tmp_path, ["--cuda-graph"] + extra)
+    b.load_checkpoint(str(tmp_path / "mid.pt"))
+    assert b.get_num_updates() == 6
+    for _ in range(6):
+        next(it_b)                       # the iterator is positioned by the caller (load_checkpoint in train.py does it)
+    for _ in range(6):
+        b.train_step([next(it_b)])
+    b.flush_stats()
+    assert b.get_num_updates() == a.get_num_updates() == 12
+    x, y = a.arena.master, b.arena.master
+    assert (x - y).abs().max().item() <= 2e-4 * x.abs().max().item()
+    ma, mb = a.optimizer.optimizer._flat_state["exp_avg"], b.optimizer.optimizer._flat_state["exp_avg"]
+    assert (ma - mb).abs().max().item() <= 2e-3 * ma.abs().max().item() + 1e-9

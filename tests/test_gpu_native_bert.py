@@ -149,3 +149,120 @@ def test_activation_recompute_gives_identical_gradients():
     l2 = nat(ids, tts, mask, mlm, nsp); l2.backward()
     assert l1.item() == l2.item()
     assert (arena.grad - g1).abs().max().item() <= 1e-3 * g1.abs().max().item()
+
+
+# ---------------------------------------------------------------------------------------------------
+# the shapes bench.py runs: H = 768, 12 heads, I = 3072, V = 30522, B * L = 4096 (one encoder layer + all heads)
+# ---------------------------------------------------------------------------------------------------
+BASE = dict(hidden_size=768, num_hidden_layers=1, num_attention_heads=12, intermediate_size=3072,
+            hidden_dropout_prob=0.0, attention_probs_dropout_prob=0.0, max_position_embeddings=512)
+
+
+def _base_models(dtype=torch.float32, vocab=30522):
+    from hetseq_9cme_b200 import bert_modeling as bm
+    from hetseq_9cme_b200.parallel.arena import ParamArena
+    torch.manual_seed(0)
+    cfg = bm.BertConfig(vocab, **BASE)
+    ref = bm.BertForPreTraining(cfg).cuda()
+    with torch.no_grad():
+        for n, p in ref.named_parameters():
+            if p.dim() == 1:
+                p.add_(torch.randn_like(p) * 0.05)
+    nat = copy.deepcopy(ref)
+    nat.cls.predictions.decoder.weight = nat.bert.embeddings.word_embeddings.weight
+    arena = ParamArena(list(nat.parameters()), groups=nat.arena_groups(), device="cuda", compute_dtype=dtype)
+    nat.bind_arena(arena)
+    nat.max_predictions_per_seq = 20
+    ref.force_torch_path = True
+    return ref, nat, arena
+
+
+def _base_batch(B, L, V, n_pred=20):
+    g = torch.Generator(device="cuda").manual_seed(7)
+    ids = torch.randint(5, V, (B, L), device="cuda", generator=g)
+    tts = torch.randint(0, 2, (B, L), device="cuda", generator=g)
+    mask = torch.ones(B, L, dtype=torch.int64, device="cuda")
+    mask[: B // 4, L - L // 5:] = 0
+    mlm = torch.full((B, L), -1, dtype=torch.int64, device="cuda")
+    for b in range(B):
+        pos = torch.randperm(L - 1, device="cuda", generator=g)[:n_pred] + 1
+        mlm[b, pos] = torch.randint(0, V, (n_pred,), device="cuda", generator=g)
+    nsp = torch.randint(0, 2, (B,), device="cuda", generator=g)
+    return ids, tts, mask, mlm, nsp
+
+
+@pytest.mark.parametrize("variant", ["default", "cta_pairs", "no_cta_pairs"])
+def test_bert_base_shapes_tf32_match_fp32_torch(variant, monkeypatch):
+    """One BERT-base layer + embeddings + MLM / NSP heads at the benchmark's sizes (4096 tokens, vocabulary 30522:
+    decoder data gradient with K = 30522 and split-K, tied-embedding weight gradient with M = 30522 and a ragged last
+    tile), TF32 kernels against the fp32 PyTorch path.  The variants force the GEMM's CTA-pair kernel on and off so
+    that both sides of the dispatch heuristic are covered at these shapes."""
+    if variant != "default":
+        monkeypatch.setenv("B200_GEMM_CTA2", "1" if variant == "cta_pairs" else "0")
+    ref, nat, arena = _base_models()
+    ids, tts, mask, mlm, nsp = _base_batch(32, 128, 30522)
+    torch.backends.cuda.matmul.allow_tf32 = False
+    ref.train(); nat.train()
+    loss_ref = ref(ids, tts, mask, mlm, nsp); loss_ref.backward()
+    loss_nat = nat(ids, tts, mask, mlm, nsp); loss_nat.backward()
+    torch.cuda.synchronize()
+    assert abs(loss_nat.item() - loss_ref.item()) / abs(loss_ref.item()) < 5e-3
+    _check_grads(ref, nat, tol=1e-2)
+    used, found = nat.last_mlm_count.tolist()
+    assert used == found == 32 * 20
+
+
+def test_bert_base_shapes_bf16_gradients_track_fp32():
+    """Same sizes in bf16 (fp32 master weights and gradient accumulators): every parameter gradient within bf16
+    tolerance of the fp32 PyTorch gradient, measured against that tensor's largest entry."""
+    ref, nat, arena = _base_models(dtype=torch.bfloat16)
+    ids, tts, mask, mlm, nsp = _base_batch(32, 128, 30522)
+    torch.backends.cuda.matmul.allow_tf32 = False
+    ref.train(); nat.train()
+    loss_ref = ref(ids, tts, mask, mlm, nsp); loss_ref.backward()
+    loss_nat = nat(ids, tts, mask, mlm, nsp); loss_nat.backward()
+    torch.cuda.synchronize()
+    assert abs(loss_nat.item() - loss_ref.item()) / abs(loss_ref.item()) < 2e-2
+    _check_grads(ref, nat, tol=6e-2)
+
+
+def test_phase2_shapes_long_sequence_attention():
+    """Sequence 512 with 80 labelled positions per sequence (phase 2): the long-sequence attention path, with ragged
+    padding, against the fp32 PyTorch path."""
+    ref, nat, arena = _base_models(vocab=4096)
+    nat.max_predictions_per_seq = 80
+    ids, tts, mask, mlm, nsp = _base_batch(4, 512, 4096, n_pred=80)
+    torch.backends.cuda.matmul.allow_tf32 = False
+    ref.train(); nat.train()
+    loss_ref = ref(ids, tts, mask, mlm, nsp); loss_ref.backward()
+    loss_nat = nat(ids, tts, mask, mlm, nsp); loss_nat.backward()
+    torch.cuda.synchronize()
+    assert abs(loss_nat.item() - loss_ref.item()) / abs(loss_ref.item()) < 5e-3
+    _check_grads(ref, nat, tol=1e-2)
+
+
+def test_tied_embedding_gradient_is_announced_last():
+    """The decoder weight is the word-embedding table: the reducer may only be told that its gradient is final after the
+    embedding backward has added the token-lookup part (otherwise that part is never summed across ranks)."""
+    from hetseq_9cme_b200.models.bert_native import GradSink
+    cfgk = dict(hidden_size=128, num_hidden_layers=2, num_attention_heads=2, intermediate_size=512,
+                hidden_dropout_prob=0.0, attention_probs_dropout_prob=0.0, max_position_embeddings=128)
+    cfg, ref, nat, arena = _models("BertForPreTraining", cfgk)
+
+    class Recorder(GradSink):
+        def __init__(self):
+            self.calls = []
+
+        def ready(self, params):
+            self.calls.append([id(p) for p in params])
+
+    rec = Recorder()
+    nat.bind_arena(arena, rec)
+    ids, tts, mask, mlm, nsp = _batch(4, 128, 1000)
+    nat.train()
+    nat(ids, tts, mask, mlm, nsp).backward()
+    emb_id = id(nat.bert.embeddings.word_embeddings.weight)
+    hits = [i for i, c in enumerate(rec.calls) if emb_id in c]
+    assert hits == [len(rec.calls) - 1], (hits, len(rec.calls))
+    every = {pid for c in rec.calls for pid in c}
+    assert every == {id(p) for p in arena.params}

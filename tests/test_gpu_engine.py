@@ -170,10 +170,9 @@ def test_loss_curve_matches_the_reference_from_its_own_checkpoint(tmp_path):
 
 def test_resume_reproduces_the_uninterrupted_run(tmp_path):
     """Train 6 steps, checkpoint, train 6 more; a fresh Controller restored from the checkpoint must reach the same
-    weights after its 6 steps (dropout on: the per-step seed is seed + num_updates, so masks are reproduced too)."""
+    weights after its 6 steps."""
     from hetseq_9cme_b200 import checkpoint_utils
-    extra = ["--hidden-dropout-override", "0.1"] if False else []
-    a, it_a = _setup(tmp_path, ["--cuda-graph"] + extra)
+    a, it_a = _setup(tmp_path, ["--cuda-graph"])
     for _ in range(6):
         a.train_step([next(it_a)])
     a.flush_stats()
@@ -184,7 +183,7 @@ def test_resume_reproduces_the_uninterrupted_run(tmp_path):
         a.train_step([next(it_a)])
     a.flush_stats()
 
-    b, it_b = _setup(tmp_path, ["--cuda-graph"] + extra)
+    b, it_b = _setup(tmp_path, ["--cuda-graph"])
     b.load_checkpoint(str(tmp_path / "mid.pt"))
     assert b.get_num_updates() == 6
     for _ in range(6):

@@ -463,8 +463,9 @@ class Controller:
     # ---- deferred (pipelined) sharded update ---------------------------------------------------------------------
     def _init_deferral(self):
         red = self._reducer
-        self._defer_update = bool(self.cuda and getattr(red, "sharded", False) and not os.environ.get("B200_NO_DEFER")
-                                  and not getattr(self.args, "no_pipelined_update", False))
+        want = bool(getattr(self.args, "pipelined_update", False) or os.environ.get("B200_PIPELINED_UPDATE")) \
+            and not os.environ.get("B200_NO_DEFER")
+        self._defer_update = bool(self.cuda and getattr(red, "sharded", False) and want)
         self._pending_hyper = None
         if self._defer_update:
             self._pend = torch.zeros(4, dtype=torch.float32, device=self.device)          # sum g^2, sample size, valid

@@ -78,10 +78,11 @@ def test_nccl_reducer_path(tmp_path):
 
 
 @needs2
-def test_pipelined_update_off_matches(tmp_path):
-    """B200_NO_DEFER=1: the sharded update at the end of the step instead of under the next forward pass."""
-    _ok(_torchrun(2, ["tools/dp_debug_run.py", str(tmp_path), "--mode", "sharded", "--graph", "--compare-single"],
-                  env=dict(SMALL_BUCKETS, B200_NO_DEFER="1")), "DP DEBUG RUN PASS")
+def test_pipelined_update_matches(tmp_path):
+    """--pipelined-update (here through its environment switch): the sharded update parked at the end of the step and
+    issued per bucket under the next forward pass; uneven shards make ranks flush and step eagerly in between."""
+    _ok(_torchrun(2, ["tools/dp_debug_run.py", str(tmp_path), "--mode", "sharded", "--graph", "--uneven", "--steps", "10",
+                      "--compare-single", "--checkpoint"], env=dict(SMALL_BUCKETS, B200_PIPELINED_UPDATE="1")), "DP DEBUG RUN PASS")
 
 
 @needs2

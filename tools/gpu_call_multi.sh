@@ -13,8 +13,8 @@ if [ -z "$NOTESTS" ]; then
 fi
 for mode in pipelined nodefer replicated; do
   case $mode in
-    pipelined) ENVS="";;
-    nodefer) ENVS="B200_NO_DEFER=1";;
+    pipelined) ENVS="B200_PIPELINED_UPDATE=1";;
+    nodefer) ENVS="";;
     replicated) ENVS="B200_NO_SHARDED=1";;
   esac
   env $ENVS timeout -k 10 300 $TR --master-port 29512 bench.py --gpus $N --steps 20 --warmup 5 > gpurun_out/bench_${N}gpu_${mode}_${TAG}.log 2>&1; echo "bench $mode rc=$?"

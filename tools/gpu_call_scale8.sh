@@ -11,9 +11,9 @@ run() {  # name, env...
   env "$@" timeout -k 10 300 $TR --master-port 29512 bench.py --gpus $N --steps 20 --warmup 5 > gpurun_out/bench_${N}gpu_${name}_${TAG}.log 2>&1; echo "bench $name rc=$?"
   tail -1 gpurun_out/bench_${N}gpu_${name}_${TAG}.log | python -c "import sys,json; d=json.loads(sys.stdin.readline()); print({k:d[k] for k in ('value','ms_per_step','final_loss','exposed_allreduce_ms_per_step','replicas_identical') if k in d}, d.get('e2e',{}).get('value'))" || tail -5 gpurun_out/bench_${N}gpu_${name}_${TAG}.log
 }
-run pipelined X=1
-run nodefer B200_NO_DEFER=1
-run nodefer_peer B200_NO_DEFER=1 B200_RS_PEER=1 B200_BCAST_PEER=1
-run nodefer_bcastpeer B200_NO_DEFER=1 B200_BCAST_PEER=1
-run pipelined_bcastpeer B200_BCAST_PEER=1
+run pipelined B200_PIPELINED_UPDATE=1
+run nodefer X=1
+run nodefer_peer B200_RS_PEER=1 B200_BCAST_PEER=1
+run nodefer_bcastpeer B200_BCAST_PEER=1
+run pipelined_bcastpeer B200_PIPELINED_UPDATE=1 B200_BCAST_PEER=1
 run replicated B200_NO_SHARDED=1

@@ -9,12 +9,12 @@ for prec in tf32 bf16; do
   timeout -k 10 300 python bench.py --steps 20 --warmup 5 --precision $prec > gpurun_out/bench_1gpu_${prec}_${TAG}.log 2>&1; echo "bench $prec rc=$?"
   tail -1 gpurun_out/bench_1gpu_${prec}_${TAG}.log | cut -c1-400
 done
-if [ -z "$SKIPNCU" ]; then
+if [ -z "$SKIPNCU" ] || [ "$SKIPNCU" = "listonly" ]; then
   CMD="python bench.py --steps 2 --warmup 3 --no-graph --no-e2e"
   $CMD > gpurun_out/plain_${TAG}.log 2>&1 &&
-  ncu --metrics gpu__time_duration.sum --clock-control none -s 1400 -c 700 --csv --log-file gpurun_out/launches_${TAG}.csv $CMD > gpurun_out/ncu_list_${TAG}.log 2>&1
+  ncu --metrics gpu__time_duration.sum --clock-control none -s 880 -c 620 --csv --log-file gpurun_out/launches_${TAG}.csv $CMD > gpurun_out/ncu_list_${TAG}.log 2>&1
   echo "ncu list rc=$?"
-  $CMD > gpurun_out/plain2_${TAG}.log 2>&1 &&
+  [ "$SKIPNCU" = "listonly" ] || { $CMD > gpurun_out/plain2_${TAG}.log 2>&1 &&
   ncu --set full --clock-control none --import-source on -k regex:'ln_fwd_kernel|ln_bwd2_kernel|adam_flat_kernel|ce_fwd_kernel|ce_bwd_kernel|embed_scatter_kernel|colsum_atomic_kernel' -s 30 -c 14 -o gpurun_out/prof_membound_${TAG} $CMD > gpurun_out/ncu_full_${TAG}.log 2>&1
-  echo "ncu full rc=$?"
+  echo "ncu full rc=$?"; }
 fi

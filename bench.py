@@ -339,7 +339,8 @@ def run_ours(a):
             for s in range(a.steps):
                 sample = next(itr)
                 fetch_ms.append((time.perf_counter() - marks[-1]) * 1e3)
-                h2d += _nbytes(sample[:1] if args.device_batch_assembly else sample)
+                from hetseq_9cme_b200.data.packed import PackedBertBatch
+                h2d += _nbytes(sample[:1] if isinstance(sample, PackedBertBatch) else sample)
                 out = controller.train_step([sample])
                 d2h += 8 * 8
                 marks.append(time.perf_counter())

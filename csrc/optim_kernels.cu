@@ -185,6 +185,31 @@ cast_f32_bf16_kernel(const float* __restrict__ src, __nv_bfloat16* __restrict__ 
   }
 }
 
+// 3xTF32 operand split: hi = x with the 13 mantissa bits a TF32 operand drops cleared, lo = (x - hi) cut the same
+// way.  hi and lo are exactly representable TF32 inputs; hi*hi' + hi*lo' + lo*hi' recovers the fp32 product to ~2^-22.
+__global__ void __launch_bounds__(256)
+split_tf32_kernel(const float* __restrict__ x, float* __restrict__ hi, float* __restrict__ lo, long long n) {
+  const long long n4 = n >> 2;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += (long long)gridDim.x * blockDim.x) {
+    const float4 v = reinterpret_cast<const float4*>(x)[i];
+    float4 h, l;
+    const float* vp = &v.x; float* hp = &h.x; float* lp = &l.x;
+#pragma unroll
+    for (int e = 0; e < 4; ++e) {
+      hp[e] = __uint_as_float(__float_as_uint(vp[e]) & 0xFFFFE000u);
+      lp[e] = __uint_as_float(__float_as_uint(vp[e] - hp[e]) & 0xFFFFE000u);
+    }
+    reinterpret_cast<float4*>(hi)[i] = h;
+    reinterpret_cast<float4*>(lo)[i] = l;
+  }
+  if (blockIdx.x == 0 && threadIdx.x < (n & 3)) {
+    const long long i = (n4 << 2) + threadIdx.x;
+    const float h = __uint_as_float(__float_as_uint(x[i]) & 0xFFFFE000u);
+    hi[i] = h;
+    lo[i] = __uint_as_float(__float_as_uint(x[i] - h) & 0xFFFFE000u);
+  }
+}
+
 static int elementwise_grid(long long work_items, int threads) {
   long long blocks = (work_items + threads - 1) / threads;
   const long long cap = (long long)num_sms() * 8;
@@ -246,5 +271,14 @@ extern "C" int b200_cast_f32_to_bf16(const float* src, void* dst, long long n, v
   if (!src || !dst) return fail(B200_ERR_ARG, "cast: null pointer");
   cast_f32_bf16_kernel<<<elementwise_grid(n / 4 + 1, 256), 256, 0, (cudaStream_t)stream>>>(src, (__nv_bfloat16*)dst, n);
   B200_LAUNCHED("cast_f32_bf16_kernel");
+  return 0;
+}
+
+extern "C" int b200_split_tf32(const float* x, float* hi, float* lo, long long n, void* stream) {
+  if (!x || !hi || !lo) return fail(B200_ERR_ARG, "split_tf32: null pointer");
+  if (((reinterpret_cast<uintptr_t>(x) | reinterpret_cast<uintptr_t>(hi) | reinterpret_cast<uintptr_t>(lo)) & 15) != 0)
+    return fail(B200_ERR_ARG, "split_tf32: buffers must be 16-byte aligned");
+  split_tf32_kernel<<<elementwise_grid(n / 4 + 1, 256), 256, 0, (cudaStream_t)stream>>>(x, hi, lo, n);
+  B200_LAUNCHED("split_tf32_kernel");
   return 0;
 }

@@ -160,7 +160,12 @@ class Controller:
         self._arena = ParamArena(params, groups=groups, device=self.device, compute_dtype=compute_dtype,
                                  bucket_bytes=bucket_bytes, alloc=alloc)
         self._reducer = build_reducer(self.args, self._arena, self.world_size, sharded=want_sharded)
-        use_native = self.cuda and not getattr(self.args, "no_native", False) and self.precision != "fp32"
+        # --precision fp32 on a GPU keeps the native kernels and switches the GEMMs to the 3xTF32 split (ops/gemm.py);
+        # --no-native (or --cpu) is what selects plain PyTorch
+        use_native = self.cuda and not getattr(self.args, "no_native", False)
+        if use_native:
+            from .ops import gemm as _gemm
+            _gemm.set_strict_fp32(self.precision == "fp32")
         if hasattr(model, "bind_arena"):
             model.bind_arena(self._arena if use_native else None, self._reducer)
         if not use_native and hasattr(model, "force_torch_path"):

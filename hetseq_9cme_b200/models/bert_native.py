@@ -125,7 +125,8 @@ def _fused_softmax(L: int) -> bool:
     import os
     # measured on B200 (profiles/README.md): at L = 128 the four epilogue warps become the bottleneck and the fused
     # form is ~6 % slower per step than the separate full-chip softmax kernels, so it is opt-in for now
-    return L <= 256 and bool(os.environ.get("B200_FUSED_SOFTMAX"))
+    from ..ops.gemm import strict_fp32
+    return L <= 256 and bool(os.environ.get("B200_FUSED_SOFTMAX")) and not strict_fp32()
 
 
 def _fused_attention(L: int, dh: int) -> bool:
@@ -137,7 +138,8 @@ def _fused_attention(L: int, dh: int) -> bool:
     (B200_FUSED_ATTN=1; it saves the 2 * B * heads * L * L activation tensors).  B200_FUSED_ATTN=0 disables it."""
     import os
     flag = os.environ.get("B200_FUSED_ATTN", "")
-    if dh != 64 or flag == "0":
+    from ..ops.gemm import strict_fp32
+    if dh != 64 or flag == "0" or strict_fp32():     # the fused kernels multiply in TF32: strict fp32 takes the GEMM path
         return False
     return L <= 128 or flag == "1"
 

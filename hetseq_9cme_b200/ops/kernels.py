@@ -90,6 +90,7 @@ def _lib():
             "b200_adadelta_flat": ([P, P, P, P, P, LL, POINTER(AdadeltaArgs), P], I),
             "b200_scale_f32": ([P, LL, F, P, P], I),
             "b200_cast_f32_to_bf16": ([P, P, LL, P], I),
+            "b200_split_tf32": ([P, P, P, LL, P], I),
             "b200_ln_bwd_scratch_bytes": ([I], LL),
             "b200_ln_fwd": ([POINTER(LnArgs), P], I),
             "b200_ln_bwd": ([POINTER(LnArgs), P], I),
@@ -213,6 +214,14 @@ def scale_(x: torch.Tensor, c: float, c_dev: Optional[torch.Tensor] = None):
     assert x.dtype == torch.float32 and x.is_contiguous()
     check(_lib().b200_scale_f32(x.data_ptr(), x.numel(), float(c), _ptr(c_dev), _stream()), "b200_scale_f32")
     return x
+
+
+def split_tf32(x: torch.Tensor):
+    """(hi, lo) TF32-exact halves of a contiguous fp32 tensor (strict-fp32 GEMM policy, see ops/gemm.py)."""
+    assert x.dtype == torch.float32 and x.is_contiguous()
+    hi, lo = torch.empty_like(x), torch.empty_like(x)
+    check(_lib().b200_split_tf32(x.data_ptr(), hi.data_ptr(), lo.data_ptr(), x.numel(), _stream()), "b200_split_tf32")
+    return hi, lo
 
 
 def cast_to_bf16(src: torch.Tensor, dst: torch.Tensor):

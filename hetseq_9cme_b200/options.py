@@ -190,7 +190,8 @@ _ENGINE = [
     (("--precision",), dict(default="tf32", choices=["tf32", "bf16", "fp32"],
                             help="tf32: fp32 storage, TF32 tensor-core math (reference parity); "
                                  "bf16: bf16 activations/weights with fp32 master weights; "
-                                 "fp32: plain PyTorch fp32 (CPU / debugging)")),
+                                 "fp32: fp32 storage and fp32-accurate products (every GEMM as three TF32 products of "
+                                 "split operands, ~3.5x the TF32 cost; plain PyTorch fp32 with --no-native / --cpu)")),
     (("--comm",), dict(default="auto", choices=["auto", "p2p", "torch"],
                        help="gradient reduction: hand-written NVLink peer kernels (p2p) or torch.distributed (torch)")),
     (("--p2p-bucket-mb",), dict(type=int, default=100, metavar="MB",
@@ -322,12 +323,12 @@ def parse_args_and_arch(parser, s=None):
     # engine switches that default to "on when the step runs on a GPU"
     for name in ("cuda_graph", "device_batch_assembly"):
         if hasattr(args, name) and getattr(args, name) is None:
-            setattr(args, name, _on_cuda(args))
+            setattr(args, name, _on_cuda(args) and (name == "cuda_graph" or getattr(args, "task", "bert") == "bert"))
     return args
 
 
 def _on_cuda(args) -> bool:
-    if getattr(args, "cpu", False) or getattr(args, "no_native", False) or getattr(args, "precision", "tf32") == "fp32":
+    if getattr(args, "cpu", False) or getattr(args, "no_native", False):
         return False
     try:
         import torch

@@ -114,6 +114,10 @@ int b200_adadelta_flat(float* p, float* g, float* square_avg, float* acc_delta, 
 /* x *= c * (c_dev ? *c_dev : 1) */
 int b200_scale_f32(float* x, long long n, float c, const float* c_dev, void* stream);
 int b200_cast_f32_to_bf16(const float* src, void* dst_bf16, long long n, void* stream);
+/* Operand split of the strict-fp32 GEMM policy (3xTF32): hi = x with the mantissa bits a TF32 operand ignores
+ * cleared, lo = the remainder cut the same way; A.B ~= Ahi.Bhi + Ahi.Blo + Alo.Bhi to about 2^-22 (the reference
+ * computes in fp32: hetseq/options.py:11).  16-byte aligned buffers. */
+int b200_split_tf32(const float* x, float* hi, float* lo, long long n, void* stream);
 
 /* ------------------------------------------------------------------------------------------------
  * Fused LayerNorm:  y = drop_post( LN( drop_pre(x + bias) + residual ) * gamma + beta )

@@ -518,3 +518,44 @@ def test_gemm_gelu_with_saved_derivative(dtype):
         scratch = torch.empty(1024, 64, device="cuda")
         got = gemm(xs, eye, act=N.ACT_GELU_SAVE_GRAD, preact_out=scratch)
         assert (got - torch.nn.functional.gelu(xs.double()).float()).abs().max().item() < 4e-3     # tf32 rounding of xs dominates
+
+
+def test_strict_fp32_gemm_is_fp32_accurate():
+    """--precision fp32: every GEMM as three TF32 products of split operands.  Against an fp64 product the error must
+    be at the fp32 level (~1e-6 of |A||B|), two to three orders below the single TF32 product, for plain, epilogue,
+    MN-major and accumulating calls."""
+    from hetseq_9cme_b200.ops import gemm as G
+    from hetseq_9cme_b200.ops import native as N
+    torch.manual_seed(3)
+    M, Nn, Kk = 384, 320, 1024
+    a = torch.randn(M, Kk, device="cuda")
+    b = torch.randn(Nn, Kk, device="cuda")
+    bias = torch.randn(Nn, device="cuda")
+    ref = a.double() @ b.double().t()
+    scale = (a.double().abs() @ b.double().abs().t()).max().item()
+    tf32 = G.gemm(a, b)
+    G.set_strict_fp32(True)
+    try:
+        strict = G.gemm(a, b)
+        e_strict = (strict.double() - ref).abs().max().item() / scale
+        e_tf32 = (tf32.double() - ref).abs().max().item() / scale
+        assert e_strict < 2e-6 and e_strict < e_tf32 / 50, (e_strict, e_tf32)
+        # bias + GELU with the saved derivative, tanh, aux add
+        u = torch.empty(M, Nn, device="cuda")
+        y = G.gemm(a, b, bias=bias, act=N.ACT_GELU_SAVE_GRAD, preact_out=u, alpha=0.05)
+        z = (ref * 0.05 + bias.double())
+        assert (y.double() - torch.nn.functional.gelu(z)).abs().max().item() < 1e-5
+        cdf = 0.5 * (1 + torch.erf(z / math.sqrt(2)))
+        assert (u.double() - (cdf + z * torch.exp(-0.5 * z * z) / math.sqrt(2 * math.pi))).abs().max().item() < 1e-5
+        aux = torch.randn(M, Nn, device="cuda")
+        w = G.gemm(a, b, aux=aux, aux_mode=N.AUX_ADD)
+        assert (w.double() - (ref + aux.double())).abs().max().item() / scale < 2e-6
+        # weight-gradient form: A and B MN-major, accumulate into an fp32 buffer
+        g = torch.randn(Kk, M, device="cuda"); x = torch.randn(Kk, Nn, device="cuda")
+        acc = torch.ones(M, Nn, device="cuda")
+        G.gemm(g, x, a_mn=True, b_mn=True, out=acc, accumulate=True)
+        want = 1.0 + g.double().t() @ x.double()
+        s2 = (g.double().abs().t() @ x.double().abs()).max().item()
+        assert (acc.double() - want).abs().max().item() / s2 < 2e-6
+    finally:
+        G.set_strict_fp32(False)

@@ -268,3 +268,24 @@ def test_tied_embedding_gradient_is_announced_last():
     assert hits == [len(rec.calls) - 1], (hits, len(rec.calls))
     every = {pid for c in rec.calls for pid in c}
     assert every == {id(p) for p in arena.params}
+
+
+def test_strict_fp32_mode_matches_fp32_torch_tightly():
+    """--precision fp32 on the native path: loss and gradients against the fp32 PyTorch path at fp32 tolerances (the
+    TF32 policy needs 2e-3 / 3e-2 on the same model)."""
+    from hetseq_9cme_b200.ops import gemm as G
+    cfgk = dict(hidden_size=128, num_hidden_layers=2, num_attention_heads=2, intermediate_size=512,
+                hidden_dropout_prob=0.0, attention_probs_dropout_prob=0.0, max_position_embeddings=128)
+    cfg, ref, nat, arena = _models("BertForPreTraining", cfgk)
+    ids, tts, mask, mlm, nsp = _batch(4, 128, 1000, pad_from=119)
+    torch.backends.cuda.matmul.allow_tf32 = False
+    ref.train(); nat.train()
+    loss_ref = ref(ids, tts, mask, mlm, nsp); loss_ref.backward()
+    G.set_strict_fp32(True)
+    try:
+        loss_nat = nat(ids, tts, mask, mlm, nsp); loss_nat.backward()
+        torch.cuda.synchronize()
+    finally:
+        G.set_strict_fp32(False)
+    assert abs(loss_nat.item() - loss_ref.item()) / abs(loss_ref.item()) < 2e-5
+    _check_grads(ref, nat, tol=5e-4)

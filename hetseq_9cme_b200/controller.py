@@ -432,7 +432,7 @@ class Controller:
             reducer.finish()
             if self.world_size > 1:
                 reducer.reduce_tail()
-        if self.world_size > 1 and getattr(reducer, "fused_norm", False):
+        if getattr(reducer, "fused_norm", False):
             from .parallel.p2p import SQ_SLOT
             norm_sq = tail[SQ_SLOT:SQ_SLOT + 1]       # summed over ranks by reduce_tail: no separate norm pass
         else:

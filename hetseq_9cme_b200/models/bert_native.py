@@ -41,6 +41,7 @@ class NativeCtx:
 
     def __init__(self, device, training: bool, sink: Optional[GradSink] = None, checkpoint_activations: bool = False):
         self.ws = K.Workspace.get(device)
+        self.side = K.SideWork.get(device)
         self.training = training
         self.sink = sink or _NULL_SINK
         self.checkpoint_activations = checkpoint_activations
@@ -260,7 +261,7 @@ class BertLayerFn(torch.autograd.Function):
             dz2 = ds2
         gemm(dz2, a, a_mn=True, b_mn=True, out=_mg(lp.W2), **wg)                                 # dW2 += dz2^T a
         du = gemm(dz2, lp.W2, b_mn=True, aux=u, aux_mode=N.AUX_MUL)                               # (dz2 W2) * gelu'(pre), u = gelu' 
-        K.colsum_(du, _mg(lp.b1), ws)
+        nctx.side.colsum_(du, _mg(lp.b1))                                                        # side stream
         gemm(du, y1, a_mn=True, b_mn=True, out=_mg(lp.W1), **wg)                                 # dW1 += du^T y1
         dy1 = gemm(du, lp.W1, b_mn=True, aux=ds2, aux_mode=N.AUX_ADD)                             # + residual branch
 
@@ -280,9 +281,10 @@ class BertLayerFn(torch.autograd.Function):
             dqkv = _attention_unfused_bwd(qkv, P, Pd, dctx, nctx, B, L, Lp, H, heads, dh, sid, p_attn)
 
         # ---- QKV projection -------------------------------------------------------------------------------
-        K.colsum_(dqkv, lp.gbqkv, ws)
+        nctx.side.colsum_(dqkv, lp.gbqkv)                                                        # side stream
         gemm(dqkv, x, a_mn=True, b_mn=True, out=lp.gWqkv, **wg)                                  # dWqkv += dqkv^T x
         dx = gemm(dqkv, lp.Wqkv, b_mn=True, aux=ds1, aux_mode=N.AUX_ADD)
+        nctx.side.join()                                  # bias gradients are in before the layer is announced
         nctx.sink.ready(lp.params)
         return dx, None, None, None, None, None, None
 

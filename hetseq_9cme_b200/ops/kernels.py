@@ -6,6 +6,8 @@ comes from :class:`Workspace` (one per device, reused by every call on the train
 """
 from __future__ import annotations
 
+import os
+
 import ctypes
 from ctypes import POINTER, byref, c_double, c_float, c_int, c_longlong, c_ulonglong, c_void_p
 from typing import Optional
@@ -402,6 +404,51 @@ def colsum_(x, out, ws: Optional[Workspace] = None, deterministic: bool = False)
         check(_lib().b200_colsum(dtype_code(x.dtype), x.data_ptr(), x.stride(0), rows, cols, out.data_ptr(), None, 0,
                                  _stream()), "b200_colsum")
     return out
+
+
+class SideWork:
+    """Memory-bound side computations that nothing downstream in the layer waits for (bias-gradient column sums) run on
+    a second stream next to the tensor-core kernels of the main stream and are joined before the layer announces its
+    gradients.  Inside a captured CUDA graph this becomes a parallel branch."""
+
+    _per_device = {}
+
+    def __init__(self, device):
+        self.device = device
+        self.stream = torch.cuda.Stream(device=device)
+        self.enabled = not os.environ.get("B200_NO_SIDE_COLSUM")
+        self._dirty = False
+        self._keep = []
+
+    @classmethod
+    def get(cls, device) -> "SideWork":
+        device = torch.device(device)
+        idx = device.index if device.index is not None else torch.cuda.current_device()
+        sw = cls._per_device.get(idx)
+        if sw is None:
+            sw = cls._per_device[idx] = SideWork(torch.device("cuda", idx))
+        return sw
+
+    def colsum_(self, x, out):
+        """out[c] += sum_r x[r, c] on the side stream (x must stay unchanged until ``join``)."""
+        if not self.enabled or (out.data_ptr() & 15):
+            return colsum_(x, out)
+        cur = torch.cuda.current_stream(self.device)
+        ev = torch.cuda.Event()
+        ev.record(cur)
+        self.stream.wait_event(ev)
+        with torch.cuda.stream(self.stream):
+            colsum_(x, out)
+        self._keep.append(x)               # its memory must not be recycled before the side stream is done with it
+        self._dirty = True
+        return out
+
+    def join(self):
+        """Make the current stream wait for everything issued on the side stream."""
+        if self._dirty:
+            torch.cuda.current_stream(self.device).wait_stream(self.stream)
+            self._dirty = False
+            self._keep.clear()
 
 
 def softmax_fwd_(S, attn_mask, B, heads, L, Lp, p_drop=0.0, seed=None, stream_id=0):

@@ -156,10 +156,48 @@ class NullReducer(BaseReducer):
         pass
 
 
+class LocalNormReducer(BaseReducer):
+    """world_size == 1 on a GPU: nothing to reduce, but the clip needs sum(g^2) over 440 MB of gradients — a 67 us
+    memory-bound pass at the end of backward.  Here each bucket's share is summed on a side stream as soon as backward
+    has produced it (same ``ready`` notifications the multi-GPU reducers use), next to the tensor-core kernels that are
+    still running, and lands in ``arena.tail[SQ_SLOT]`` like the reducers' fused norm."""
+
+    def __init__(self, arena):
+        super().__init__(arena, 1)
+        self.fused_norm = True
+        self._side = torch.cuda.Stream(device=arena.device)
+        from .p2p import SQ_SLOT
+        self._sq = arena.tail[SQ_SLOT:SQ_SLOT + 1]
+
+    def begin(self, sync_now: bool):
+        super().begin(sync_now)
+        self._active = sync_now            # the base class only goes active for world_size > 1
+
+    def _launch(self, bi):
+        from ..ops import kernels
+        self._launched.add(bi)
+        s, e, _ = self.arena.buckets[bi]
+        # always on the side stream: the launches share one scratch buffer and must not overlap each other
+        ev = torch.cuda.Event()
+        ev.record(torch.cuda.current_stream())
+        self._side.wait_event(ev)
+        with torch.cuda.stream(self._side):
+            kernels.sumsq(self.arena.grad[s:e], self._sq, accumulate=True)
+
+    def _wait_all(self):
+        torch.cuda.current_stream().wait_stream(self._side)
+
+    def reduce_tail(self):
+        pass
+
+
 def build_reducer(args, arena, world_size: int, sharded: bool = False):
     """Pick the back end.  Every rank must end up with the SAME kind of reducer (they issue different collectives),
     so a failure on one rank is agreed on by all before anyone falls back."""
     if world_size <= 1:
+        import os
+        if arena.device.type == "cuda" and not os.environ.get("B200_NO_LOCAL_NORM"):
+            return LocalNormReducer(arena)
         return NullReducer(arena, 1)
     comm = getattr(args, "comm", "auto")
     if arena.device.type == "cuda" and comm in ("auto", "p2p"):

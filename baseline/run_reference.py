@@ -115,7 +115,7 @@ def run_reference(a):
             cfg_path = synthetic.write_bert_config(os.path.join(tmp, "bert_config.json"), vocab_size=20005, **MODELS[a.model])
             argv = ["--data", tmp, "--dict", paths["vocab"], "--config_file", cfg_path, "--train_file", paths["train"],
                     "--validation_file", paths["validation"], "--test_file", paths["test"], "--extension_file", "conll2003",
-                    "--num-workers", "2"] + common
+                    "--num-workers", "2", "--find-unused-parameters"] + common      # as its own script passes it (the pooler is unused)
             parser = options.get_training_parser(task="BertForTokenClassification", optimizer="adam",
                                                  lr_scheduler="PolynomialDecayScheduler")
             task_cls = importlib.import_module("hetseq.tasks.bert_for_token_classification_task").BertForTokenClassificationTask
@@ -220,6 +220,7 @@ def run_reference(a):
             sys.__stdout__.flush()
         if world > 1:
             dist.barrier()
+            dist.destroy_process_group()
     except Exception as e:
         import traceback
         traceback.print_exc(file=sys.stderr)

@@ -18,3 +18,12 @@ if [ -z "$SKIPNCU" ] || [ "$SKIPNCU" = "listonly" ]; then
   ncu --set full --clock-control none --import-source on -k regex:'ln_fwd_kernel|ln_bwd2_kernel|adam_flat_kernel|ce_fwd_kernel|ce_bwd_kernel|embed_scatter_kernel|colsum_atomic_kernel' -s 30 -c 14 -o gpurun_out/prof_membound_${TAG} $CMD > gpurun_out/ncu_full_${TAG}.log 2>&1
   echo "ncu full rc=$?"; }
 fi
+# BASELINE config 5 on one GPU, both arms
+timeout -k 10 400 python bench.py --steps 20 --warmup 5 --task ner > gpurun_out/bench_c5_ours_tf32_1gpu_${TAG}.log 2>&1; echo "ner ours rc=$?"
+grep -E '^\{' gpurun_out/bench_c5_ours_tf32_1gpu_${TAG}.log | tail -1 | cut -c1-330
+timeout -k 10 400 python bench.py --steps 20 --warmup 5 --task ner --impl reference > gpurun_out/bench_c5_ref_1gpu_${TAG}.log 2>&1; echo "ner ref rc=$?"
+grep -E '^\{' gpurun_out/bench_c5_ref_1gpu_${TAG}.log | tail -1 | cut -c1-330
+for v in B200_NO_SIDE_COLSUM B200_NO_LOCAL_NORM; do
+  env $v=1 timeout -k 10 300 python bench.py --steps 20 --warmup 5 > gpurun_out/bench_1gpu_${v}_${TAG}.log 2>&1
+  echo "$v: $(grep -E '^\{' gpurun_out/bench_1gpu_${v}_${TAG}.log | tail -1 | cut -c1-200)"
+done

@@ -748,7 +748,9 @@ class Controller:
         g = torch.cuda.CUDAGraph()
         self._model.train()
         before = native.launch_count()
-        with torch.cuda.graph(g, pool=self._graph_pool):      # replays are serial, so all shapes share one pool
+        # replays are serial, so all shapes share one pool.  thread_local: the loader threads keep pinning host memory
+        # while this thread captures — in the default (global) mode such a call from ANY thread invalidates the capture
+        with torch.cuda.graph(g, pool=self._graph_pool, capture_error_mode="thread_local"):
             self._graph_body(st)
         st["launches"] = native.launch_count() - before        # kernels of ours inside one replay
         native.add_launch_count(-st["launches"])                # capture recorded them, it did not run them

@@ -407,16 +407,18 @@ def colsum_(x, out, ws: Optional[Workspace] = None, deterministic: bool = False)
 
 
 class SideWork:
-    """Memory-bound side computations that nothing downstream in the layer waits for (bias-gradient column sums) run on
-    a second stream next to the tensor-core kernels of the main stream and are joined before the layer announces its
-    gradients.  Inside a captured CUDA graph this becomes a parallel branch."""
+    """Memory-bound side computations that nothing downstream in the layer waits for (bias-gradient column sums) can run
+    on a second stream next to the tensor-core kernels of the main stream, joined before the layer announces its
+    gradients; inside a captured CUDA graph this becomes a parallel branch.  Measured on B200 (profiles/README.md §18):
+    the 24 fork / join pairs per step cost more than the ~10 us kernels they hide (7.83 vs 7.70 ms / step), so it is
+    opt-in: B200_SIDE_COLSUM=1."""
 
     _per_device = {}
 
     def __init__(self, device):
         self.device = device
         self.stream = torch.cuda.Stream(device=device)
-        self.enabled = not os.environ.get("B200_NO_SIDE_COLSUM")
+        self.enabled = bool(os.environ.get("B200_SIDE_COLSUM"))
         self._dirty = False
         self._keep = []
 

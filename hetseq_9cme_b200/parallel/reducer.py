@@ -160,7 +160,9 @@ class LocalNormReducer(BaseReducer):
     """world_size == 1 on a GPU: nothing to reduce, but the clip needs sum(g^2) over 440 MB of gradients — a 67 us
     memory-bound pass at the end of backward.  Here each bucket's share is summed on a side stream as soon as backward
     has produced it (same ``ready`` notifications the multi-GPU reducers use), next to the tensor-core kernels that are
-    still running, and lands in ``arena.tail[SQ_SLOT]`` like the reducers' fused norm."""
+    still running, and lands in ``arena.tail[SQ_SLOT]`` like the reducers' fused norm.  Measured on B200
+    (profiles/README.md §18): 18 small launches with their fork / join edges in the captured graph are slower than the
+    one pass they replace (7.89 vs 7.70 ms / step) — opt-in with B200_LOCAL_NORM=1."""
 
     def __init__(self, arena):
         super().__init__(arena, 1)
@@ -196,7 +198,7 @@ def build_reducer(args, arena, world_size: int, sharded: bool = False):
     so a failure on one rank is agreed on by all before anyone falls back."""
     if world_size <= 1:
         import os
-        if arena.device.type == "cuda" and not os.environ.get("B200_NO_LOCAL_NORM"):
+        if arena.device.type == "cuda" and os.environ.get("B200_LOCAL_NORM"):
             return LocalNormReducer(arena)
         return NullReducer(arena, 1)
     comm = getattr(args, "comm", "auto")

@@ -23,7 +23,8 @@ timeout -k 10 400 python bench.py --steps 20 --warmup 5 --task ner > gpurun_out/
 grep -E '^\{' gpurun_out/bench_c5_ours_tf32_1gpu_${TAG}.log | tail -1 | cut -c1-330
 timeout -k 10 400 python bench.py --steps 20 --warmup 5 --task ner --impl reference > gpurun_out/bench_c5_ref_1gpu_${TAG}.log 2>&1; echo "ner ref rc=$?"
 grep -E '^\{' gpurun_out/bench_c5_ref_1gpu_${TAG}.log | tail -1 | cut -c1-330
-for v in B200_NO_SIDE_COLSUM B200_NO_LOCAL_NORM; do
-  env $v=1 timeout -k 10 300 python bench.py --steps 20 --warmup 5 > gpurun_out/bench_1gpu_${v}_${TAG}.log 2>&1
+for v in B200_SIDE_COLSUM B200_LOCAL_NORM B200_GEMM_CTA2; do
+  PREC=tf32; [ $v = B200_GEMM_CTA2 ] && PREC=bf16
+  env $v=1 timeout -k 10 300 python bench.py --steps 20 --warmup 5 --precision $PREC > gpurun_out/bench_1gpu_${v}_${TAG}.log 2>&1
   echo "$v: $(grep -E '^\{' gpurun_out/bench_1gpu_${v}_${TAG}.log | tail -1 | cut -c1-200)"
 done

@@ -54,6 +54,34 @@ class _ArenaMixin:
     def has_arena(self) -> bool:
         return getattr(self, "arena", None) is not None
 
+    def _load_state_exact(self, state_dict):
+        """``load_state_dict`` for the arena path.  torch's implementation casts every state tensor to the dtype of its
+        parameter — in bf16 mode that is the bf16 working copy, which would round the fp32 moments to 8 bits on every
+        resume.  Here the hyper-parameters go through torch (empty state) and the moments are copied into the flat
+        fp32 buffers as they are."""
+        groups = state_dict["param_groups"]
+        saved_ids = [pid for g in groups for pid in g["params"]]
+        ours = [p for g in self.param_groups for p in g["params"]]
+        if len(saved_ids) != len(ours):
+            raise ValueError("loaded state dict has a different number of parameters ({} vs {})".format(len(saved_ids), len(ours)))
+        torch.optim.Optimizer.load_state_dict(self, {"state": {}, "param_groups": groups})
+        arena = self.arena
+        steps = []
+        for pid, p in zip(saved_ids, ours):
+            saved = state_dict["state"].get(pid, {})
+            o, n = arena.offsets[id(p)], p.numel()
+            st = self.state[p]
+            for name in self._state_names:
+                flat = self._flat_state[name][o:o + n].view(p.shape)
+                if name in saved:
+                    flat.copy_(saved[name].to(device=flat.device, dtype=torch.float32).reshape(p.shape))
+                else:
+                    flat.zero_()
+                st[name] = flat
+            st["step"] = int(saved.get("step", 0))
+            steps.append(st["step"])
+        self._global_step = max(steps) if steps else 0
+
     def _load_flat_state(self):
         """After ``load_state_dict`` the per-parameter tensors are fresh copies: move them back into the flat
         buffers and re-establish the views."""
@@ -198,9 +226,9 @@ class Adam(_ArenaMixin, torch.optim.Optimizer):
             self.state[p]["step"] = self._global_step
 
     def load_state_dict(self, state_dict):
-        super().load_state_dict(state_dict)
         if self.has_arena:
-            self._load_flat_state()
+            return self._load_state_exact(state_dict)
+        super().load_state_dict(state_dict)
 
 
 class Adadelta(_ArenaMixin, torch.optim.Optimizer):
@@ -273,9 +301,9 @@ class Adadelta(_ArenaMixin, torch.optim.Optimizer):
             self.state[p]["step"] = self._global_step
 
     def load_state_dict(self, state_dict):
-        super().load_state_dict(state_dict)
         if self.has_arena:
-            self._load_flat_state()
+            return self._load_state_exact(state_dict)
+        super().load_state_dict(state_dict)
 
 
 # -------------------------------------------------------------------------------------------------

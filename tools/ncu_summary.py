@@ -30,8 +30,11 @@ def main(rep):
             v = r[idx[h]]
             if n == "kernel":
                 v = v.split("(")[0].replace("void ", "").replace("b200::", "")[:60]
-            elif n == "us" and units[idx[h]] in ("ns", "nsecond"):
-                v = "%.2f" % (float(v.replace(",", "")) / 1e3)
+            elif n == "us":
+                v = "%.2f" % (float(v.replace(",", "")) * {"ns": 1e-3, "nsecond": 1e-3, "us": 1.0, "usecond": 1.0, "ms": 1e3,
+                                                           "msecond": 1e3}.get(units[idx[h]], 1.0))
+            elif n.endswith("_MB"):
+                v = "%.2f" % (float(v.replace(",", "")) * {"byte": 1e-6, "Kbyte": 1e-3, "Mbyte": 1.0, "Gbyte": 1e3}.get(units[idx[h]], 1.0))
             else:
                 try:
                     v = "%.2f" % float(v.replace(",", ""))

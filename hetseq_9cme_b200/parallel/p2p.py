@@ -104,8 +104,14 @@ class CommRuntime:
             tag[0] = "%d.%x" % (os.getpid(), time.time_ns() & 0xFFFFFFFFFF)
         dist.broadcast_object_list(tag, src=0)
         inst, err = None, ""
+        hosts = [None] * world
+        dist.all_gather_object(hosts, _hostname())
         if os.environ.get("B200_COMM", "own") != "own":
             err = "disabled by B200_COMM"
+        elif world > MAX_RANKS or len(set(hosts)) > 1:
+            # Unix sockets and peer mappings end at the host: decided from facts every rank sees, so nobody waits for a
+            # rendezvous that cannot happen
+            err = "ranks span %d hosts / %d ranks: one NVSwitch domain of at most %d ranks is required" % (len(set(hosts)), world, MAX_RANKS)
         else:
             try:
                 inst = cls(rank, world, tag[0])

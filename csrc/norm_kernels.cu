@@ -16,7 +16,8 @@ namespace b200 {
 
 constexpr int kLnWarps = 8;
 constexpr int kLnThreads = kLnWarps * 32;
-constexpr int kLnBwdMaxBlocks = 296;  // 2 per SM
+constexpr int kLnBwdMaxBlocks = 296;   // 2 per SM
+constexpr int kLnBwdMaxBlocks3 = 444;  // 3 per SM (ln_bwd2_kernel<..., 3>)
 
 template <typename T>
 struct LnCommon {
@@ -200,8 +201,10 @@ struct LnDirect {
 // Two warps per row: halves the per-thread column accumulators (register pressure was capping the one-warp
 // version at one block per SM).  Block = 8 warps = 4 rows per iteration; row statistics are combined through
 // shared memory (double-buffered by iteration parity -> one __syncthreads per iteration).  cols % 256 == 0.
-template <typename T, int NVH>
-__global__ void __launch_bounds__(kLnThreads, 2)
+// OCC = CTAs per SM the register allocation is held to: 2 -> 128 registers (no spills), 3 -> 80 registers and ~70 bytes
+// of spills per thread but half as many warps again to hide the load -> reduce -> store chain behind.
+template <typename T, int NVH, int OCC>
+__global__ void __launch_bounds__(kLnThreads, OCC)
 ln_bwd2_kernel(const LnCommon<T> a, const T* __restrict__ dy, long long lddy, const float* __restrict__ mean_in,
                const float* __restrict__ rstd_in, T* __restrict__ ds, long long ldds, T* __restrict__ dz, long long lddz,
                float* __restrict__ scratch, int want_dbias, const LnDirect direct) {
@@ -380,16 +383,24 @@ static int ln_bwd_t(const b200_ln_args* a, cudaStream_t st) {
   const LnCommon<T> c = make_common<T>(a);
   if ((a->cols & 255) == 0) {
     // two warps per row
+    static const int occ = [] { const char* e = getenv("B200_LN_BWD_OCC"); const int v = e ? atoi(e) : 3; return v == 2 ? 2 : 3; }();
     int blocks = (a->rows + 3) / 4;
-    if (blocks > kLnBwdMaxBlocks) blocks = kLnBwdMaxBlocks;
+    const int cap = occ == 2 ? kLnBwdMaxBlocks : kLnBwdMaxBlocks3;
+    if (blocks > cap) blocks = cap;
     if (blocks < 1) blocks = 1;
     const size_t smem2 = (size_t)4 * a->cols * sizeof(float);
     const int want = a->dbias != nullptr;
     const bool direct_mode = a->scratch == nullptr;
     const LnDirect direct{a->dgamma, a->dbeta, a->dbias};
 #define LN_BWD2(NVH)                                                                                                  \
-  launch_pdl(ln_bwd2_kernel<T, NVH>, dim3(blocks), dim3(kLnThreads), smem2, st, 1, c, (const T*)a->dy, a->lddy, a->mean,  \
-             a->rstd, (T*)a->ds, a->ldds, (T*)a->dz, a->lddz, (float*)a->scratch, want, direct)
+  do {                                                                                                                \
+    if (occ == 2)                                                                                                     \
+      launch_pdl(ln_bwd2_kernel<T, NVH, 2>, dim3(blocks), dim3(kLnThreads), smem2, st, 1, c, (const T*)a->dy, a->lddy, \
+                 a->mean, a->rstd, (T*)a->ds, a->ldds, (T*)a->dz, a->lddz, (float*)a->scratch, want, direct);         \
+    else                                                                                                              \
+      launch_pdl(ln_bwd2_kernel<T, NVH, 3>, dim3(blocks), dim3(kLnThreads), smem2, st, 1, c, (const T*)a->dy, a->lddy, \
+                 a->mean, a->rstd, (T*)a->ds, a->ldds, (T*)a->dz, a->lddz, (float*)a->scratch, want, direct);         \
+  } while (0)
     switch (a->cols / 256) {
       case 1: LN_BWD2(1); break;
       case 2: LN_BWD2(2); break;
@@ -425,7 +436,7 @@ static int ln_bwd_t(const b200_ln_args* a, cudaStream_t st) {
 
 using namespace b200;
 
-extern "C" long long b200_ln_bwd_scratch_bytes(int cols) { return (long long)kLnBwdMaxBlocks * 3 * cols * 4; }
+extern "C" long long b200_ln_bwd_scratch_bytes(int cols) { return (long long)kLnBwdMaxBlocks3 * 3 * cols * 4; }
 
 extern "C" int b200_ln_fwd(const b200_ln_args* a, void* stream) {
   int rc = check_ln(a);

@@ -196,3 +196,35 @@ def test_resume_reproduces_the_uninterrupted_run(tmp_path):
     assert (x - y).abs().max().item() <= 2e-4 * x.abs().max().item()
     ma, mb = a.optimizer.optimizer._flat_state["exp_avg"], b.optimizer.optimizer._flat_state["exp_avg"]
     assert (ma - mb).abs().max().item() <= 2e-3 * ma.abs().max().item() + 1e-9
+
+
+@pytest.mark.parametrize("graph", [False, True])
+def test_mnist_task_trains_on_the_gpu(tmp_path, graph):
+    """The plumbing example on a GPU: a plain torch CNN through the arena, the fused Adadelta step and (by default) the
+    captured step; the loss must fall."""
+    from hetseq_9cme_b200 import options, tasks
+    from hetseq_9cme_b200.controller import Controller
+    from hetseq_9cme_b200.data import synthetic
+    d = str(tmp_path)
+    synthetic.make_mnist(d, 64 * 12, 64)
+    argv = ["--task", "mnist", "--optimizer", "adadelta", "--data", d, "--max-sentences", "64", "--lr", "1.0", "--clip-norm", "100",
+            "--valid-subset", "test", "--save-dir", d + "/ck", "--distributed-world-size", "1", "--num-workers", "0",
+            "--log-format", "none", "--fast-stat-sync", "--warmup-updates", "0", "--total-num-update", "1000",
+            "--cuda-graph" if graph else "--no-cuda-graph"]
+    args = options.parse_training_args(argv)
+    torch.manual_seed(0)
+    task = tasks.MNISTTask.setup_task(args)
+    task.load_dataset("test")
+    c = Controller(args, task, task.build_model(args))
+    it = c.get_train_iterator(epoch=0, load_dataset=True)
+    c.lr_step(it.epoch)
+    losses = []
+    for epoch in range(3):
+        for s in it.next_epoch_itr(shuffle=False):
+            c.train_step([s])
+            c.flush_stats()
+            losses.append(c.get_meter("train_loss").val)
+    assert c.get_num_updates() == 36 and (c._graph is not None) == graph
+    assert losses[-1] < 0.5 * losses[0], (losses[0], losses[-1])
+    out = c.valid_step(next(iter(it.next_epoch_itr(shuffle=False))))
+    assert out["sample_size"] > 0 and out["loss"] == out["loss"]

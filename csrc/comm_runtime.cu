@@ -432,8 +432,12 @@ extern "C" int b200_comm_alloc(void* comm, long long bytes, int want_multicast, 
         uint64_t added = 0;
         rc = barrier(c, 1, &added);
         if (rc) return bail(rc);
-        r = d.MulticastBindMem(b->mc, 0, b->own, 0, b->bytes, 0);
-        if (r == CUDA_SUCCESS) b->mc_bound = true;
+        if (added & 1u) {                             // every rank added its device (a bind would otherwise block for ever)
+          r = d.MulticastBindMem(b->mc, 0, b->own, 0, b->bytes, 0);
+          if (r == CUDA_SUCCESS) b->mc_bound = true;
+        } else {
+          r = CUDA_ERROR_NOT_READY;
+        }
       } else {
         rc = barrier(c, 0, nullptr);                  // keep the round count equal on every rank
         if (rc) return bail(rc);

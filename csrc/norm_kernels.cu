@@ -202,7 +202,9 @@ struct LnDirect {
 // version at one block per SM).  Block = 8 warps = 4 rows per iteration; row statistics are combined through
 // shared memory (double-buffered by iteration parity -> one __syncthreads per iteration).  cols % 256 == 0.
 // OCC = CTAs per SM the register allocation is held to: 2 -> 128 registers (no spills), 3 -> 80 registers and ~70 bytes
-// of spills per thread but half as many warps again to hide the load -> reduce -> store chain behind.
+// of spills per thread but half as many warps again to hide the load -> reduce -> store chain behind.  Measured on the
+// BERT-base step (B200, 30 steps, twice each): 7.670 ms with 2, 7.712 ms with 3 — the spills cost more than the extra
+// warps hide — so 2 is the default and B200_LN_BWD_OCC=3 selects the other instantiation.
 template <typename T, int NVH, int OCC>
 __global__ void __launch_bounds__(kLnThreads, OCC)
 ln_bwd2_kernel(const LnCommon<T> a, const T* __restrict__ dy, long long lddy, const float* __restrict__ mean_in,
@@ -383,7 +385,7 @@ static int ln_bwd_t(const b200_ln_args* a, cudaStream_t st) {
   const LnCommon<T> c = make_common<T>(a);
   if ((a->cols & 255) == 0) {
     // two warps per row
-    static const int occ = [] { const char* e = getenv("B200_LN_BWD_OCC"); const int v = e ? atoi(e) : 3; return v == 2 ? 2 : 3; }();
+    static const int occ = [] { const char* e = getenv("B200_LN_BWD_OCC"); const int v = e ? atoi(e) : 2; return v == 3 ? 3 : 2; }();
     int blocks = (a->rows + 3) / 4;
     const int cap = occ == 2 ? kLnBwdMaxBlocks : kLnBwdMaxBlocks3;
     if (blocks > cap) blocks = cap;

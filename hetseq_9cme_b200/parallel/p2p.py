@@ -240,15 +240,15 @@ class P2PReducer(BaseReducer):
         # CTA width of the launches that overlap backward (see b200_p2p_allreduce: threads * 1000 + blocks)
         self.threads = int(os.environ.get("B200_P2P_THREADS", 512))
         self.no_overlap = bool(os.environ.get("B200_P2P_NO_OVERLAP"))
-        # data paths of the sharded mode: NVLS (multimem) or plain peer loads / stores.  In-switch reduction keeps the
-        # inbound traffic of a reduce-scatter at S/W, a multicast store keeps the outbound traffic of the broadcast at
-        # S/W — but both loop this rank's own share through the switch as well; B200_RS_PEER / B200_BCAST_PEER select
-        # the peer forms (measured per rank count in profiles/README.md)
-        # update kernels that run NEXT TO the forward pass: few CTAs (they are NVLink-bound, and every extra resident
-        # warp takes issue slots from the persistent GEMM CTA of its SM)
+        # update kernels that run NEXT TO the forward pass (--pipelined-update): few CTAs — they are NVLink-bound, and
+        # every extra resident warp takes issue slots from the persistent GEMM CTA of its SM
         self.pipelined_blocks = int(os.environ.get("B200_PIPELINED_BLOCKS", "148"))
-        # Measured (tools/gpu_probe_p2p.py, 150.7 MB arena): 2 GPUs — reduce-scatter 0.25 ms with peer loads vs 0.34 ms
-        # through the switch, Adam + broadcast 0.147 vs 0.245 ms; 8 GPUs — all forms within 5 % (0.32 / 0.23 ms).
+        # Data paths of the sharded mode: NVLS (multimem) or plain peer loads / stores.  In-switch reduction keeps the
+        # inbound traffic of a reduce-scatter at S/W and a multicast store keeps the outbound traffic of the broadcast
+        # at S/W — but both loop this rank's own share through the switch as well.  Measured (tools/gpu_probe_p2p.py,
+        # 150.7 MB arena): 2 GPUs — reduce-scatter 0.25 ms with peer loads vs 0.34 ms through the switch, Adam +
+        # broadcast 0.147 vs 0.245 ms; 8 GPUs — all forms within 5 % (0.32 / 0.23 ms).  B200_RS_PEER / B200_BCAST_PEER
+        # = 0 / 1 override the choice.
         small = world_size <= 4
         self.rs_peer = _env_flag("B200_RS_PEER", small)
         self.bcast_peer = _env_flag("B200_BCAST_PEER", small)

@@ -26,6 +26,7 @@
 #include <vector>
 
 #include <poll.h>
+#include <sys/mman.h>
 #include <sys/socket.h>
 #include <sys/un.h>
 #include <time.h>
@@ -267,6 +268,20 @@ int barrier(Comm* c, uint64_t word0, uint64_t* and_out) {
   return 0;
 }
 
+int open_listener(Comm* c) {
+  c->listen_fd = socket(AF_UNIX, SOCK_STREAM | SOCK_CLOEXEC, 0);
+  if (c->listen_fd < 0) return fail(B200_ERR_STATE, "comm_init: socket(): %s", strerror(errno));
+  sockaddr_un addr;
+  const socklen_t len = make_addr(addr, c->tag, c->rank);
+  if (bind(c->listen_fd, reinterpret_cast<sockaddr*>(&addr), len) != 0 || listen(c->listen_fd, 64) != 0) {
+    const int e = errno;
+    close(c->listen_fd);
+    c->listen_fd = -1;
+    return fail(B200_ERR_STATE, "comm_init: bind/listen: %s", strerror(e));
+  }
+  return 0;
+}
+
 size_t round_up(size_t n, size_t a) { return (n + a - 1) / a * a; }
 
 void release_buffer(Comm* c, Buffer* b) {
@@ -304,16 +319,7 @@ extern "C" int b200_comm_init(int rank, int world, const char* tag, int timeout_
   d.DeviceGetAttribute(&fd_ok, CU_DEVICE_ATTRIBUTE_HANDLE_TYPE_POSIX_FILE_DESCRIPTOR_SUPPORTED, c->cu_dev);
   if (d.multicast_api) d.DeviceGetAttribute(&mc_ok, CU_DEVICE_ATTRIBUTE_MULTICAST_SUPPORTED, c->cu_dev);
   if (getenv("B200_NO_NVLS")) mc_ok = 0;
-  c->listen_fd = socket(AF_UNIX, SOCK_STREAM | SOCK_CLOEXEC, 0);
-  if (c->listen_fd < 0) { delete c; return fail(B200_ERR_STATE, "comm_init: socket(): %s", strerror(errno)); }
-  sockaddr_un addr;
-  const socklen_t len = make_addr(addr, c->tag, rank);
-  if (bind(c->listen_fd, reinterpret_cast<sockaddr*>(&addr), len) != 0 || listen(c->listen_fd, 64) != 0) {
-    const int e = errno;
-    close(c->listen_fd);
-    delete c;
-    return fail(B200_ERR_STATE, "comm_init: bind/listen: %s", strerror(e));
-  }
+  if (const int lrc = open_listener(c)) { delete c; return lrc; }
   uint64_t all = 0;
   const uint64_t caps = (fd_ok ? 1u : 0u) | (mc_ok ? 2u : 0u);
   const int rc = world > 1 ? barrier(c, caps, &all) : 0;
@@ -323,6 +329,57 @@ extern "C" int b200_comm_init(int rank, int world, const char* tag, int timeout_
   c->multicast = (all & 2u) != 0 && world > 1;
   *comm_out = c;
   return 0;
+}
+
+// Control-plane self-test, no GPU needed (tests/test_native_host.py runs it with three processes): rendezvous, an
+// AND-agreement round, one descriptor per rank passed to every peer as SCM_RIGHTS (a memfd holding a known
+// word, read back through the received descriptor), and two rounds with one rank lagging, so that a message of
+// the next round can arrive before the current one is complete (the stash).
+extern "C" int b200_comm_selftest(int rank, int world, const char* tag, int timeout_ms) {
+  if (!tag || world < 1 || world > kMaxRanks || rank < 0 || rank >= world) return fail(B200_ERR_ARG, "comm_selftest: bad argument");
+  Comm comm;
+  Comm* c = &comm;
+  c->rank = rank; c->world = world; c->tag = tag;
+  if (timeout_ms > 0) c->timeout_ms = timeout_ms;
+  if (const int rc = open_listener(c)) return rc;
+  auto done = [&](int code) {
+    for (auto& s : c->stash) for (int k = 0; k < 2; ++k) if (s.fds[k] >= 0) close(s.fds[k]);
+    close(c->listen_fd);
+    return code;
+  };
+  if (world == 1) return done(0);
+  uint64_t all = 0;
+  int rc = barrier(c, ~(1ull << rank), &all);
+  if (rc) return done(rc);
+  if (all != ~((1ull << world) - 1)) return done(fail(B200_ERR_STATE, "comm_selftest: agreement word %llx", (unsigned long long)all));
+  const int mfd = memfd_create("b200seq.selftest", MFD_CLOEXEC);
+  if (mfd < 0) return done(fail(B200_ERR_STATE, "comm_selftest: memfd_create: %s", strerror(errno)));
+  const uint64_t token = 0xB200000000000000ull | (uint64_t)(rank * 1000 + 7);
+  if (write(mfd, &token, sizeof(token)) != (ssize_t)sizeof(token)) { close(mfd); return done(fail(B200_ERR_STATE, "comm_selftest: write")); }
+  Msg mine[kMaxRanks] = {};
+  int fds[kMaxRanks][2];
+  Stashed in[kMaxRanks];
+  for (int p = 0; p < world; ++p) { mine[p].word[0] = (uint64_t)(rank * 16 + p); mine[p].nfds = 1; fds[p][0] = mfd; fds[p][1] = -1; }
+  rc = exchange(c, mine, fds, in);
+  close(mfd);
+  if (rc) return done(rc);
+  for (int p = 0; p < world; ++p) {
+    if (p == rank) continue;
+    uint64_t got = 0;
+    const ssize_t n = pread(in[p].fds[0], &got, sizeof(got), 0);
+    close(in[p].fds[0]);
+    if (in[p].m.word[0] != (uint64_t)(p * 16 + rank)) return done(fail(B200_ERR_STATE, "comm_selftest: wrong payload from rank %d", p));
+    if (n != (ssize_t)sizeof(got) || got != (0xB200000000000000ull | (uint64_t)(p * 1000 + 7)))
+      return done(fail(B200_ERR_STATE, "comm_selftest: descriptor from rank %d does not read back", p));
+  }
+  // the last rank lags: a peer that completes a round first may deliver its next message early (stashed here)
+  if (rank == world - 1) usleep(200000);
+  for (int round = 0; round < 2; ++round) {
+    rc = barrier(c, (uint64_t)(round + 1), &all);
+    if (rc) return done(rc);
+    if (all != (uint64_t)(round + 1)) return done(fail(B200_ERR_STATE, "comm_selftest: round %d word %llx", round, (unsigned long long)all));
+  }
+  return done(0);
 }
 
 extern "C" int b200_comm_multicast_supported(void* comm) { return comm && static_cast<Comm*>(comm)->multicast ? 1 : 0; }

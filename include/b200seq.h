@@ -330,6 +330,8 @@ typedef struct {
 int b200_comm_init(int rank, int world, const char* tag, int timeout_ms, void** comm_out);
 int b200_comm_multicast_supported(void* comm);
 int b200_comm_barrier(void* comm);
+/* Control-plane self-test without a GPU: rendezvous, agreement, descriptor passing, out-of-order rounds. */
+int b200_comm_selftest(int rank, int world, const char* tag, int timeout_ms);
 int b200_comm_alloc(void* comm, long long bytes, int want_multicast, b200_comm_buffer* out);   /* collective */
 int b200_comm_free(void* comm, void* handle);
 int b200_comm_destroy(void* comm);

@@ -69,3 +69,44 @@ def test_two_ranks_equal_one_rank_with_accumulation(tmp_path):
         os.environ.pop("B200SEQ_TEST_NO_DROPOUT", None)
     for k in two:
         assert torch.allclose(two[k], one[k], atol=2e-5), k
+
+
+def _comm_selftest_worker(rank, world, tag, out_dir):
+    import ctypes
+    from hetseq_9cme_b200.ops import native
+    lib = native.cuda_lib()
+    lib.b200_comm_selftest.argtypes = [ctypes.c_int, ctypes.c_int, ctypes.c_char_p, ctypes.c_int]
+    rc = lib.b200_comm_selftest(rank, world, tag.encode(), 20000)
+    msg = lib.b200_last_error()
+    with open(os.path.join(out_dir, f"rc{rank}"), "w") as f:
+        f.write(f"{rc} {msg.decode() if rc and msg else ''}")
+
+
+@pytest.mark.parametrize("world", [1, 3])
+def test_comm_runtime_control_plane(tmp_path, world):
+    """The runtime's host side without a GPU (csrc/comm_runtime.cu: b200_comm_selftest): rendezvous over abstract
+    Unix sockets, AND-agreement, descriptors passed as SCM_RIGHTS and read back, rounds arriving out of order.
+    The same code carries the CUDA VMM handles on a GPU box (tests/test_gpu_multi.py)."""
+    from hetseq_9cme_b200.ops import native
+    if not native.cuda_lib_available():
+        pytest.skip("libb200seq.so not built")
+    tag = f"selftest.{os.getpid()}.{world}"
+    d = str(tmp_path)
+    if world == 1:
+        _comm_selftest_worker(0, 1, tag, d)
+    else:
+        mp.spawn(_comm_selftest_worker, args=(world, tag, d), nprocs=world, join=True)
+    for r in range(world):
+        assert open(os.path.join(d, f"rc{r}")).read().split(" ", 1)[0] == "0", open(os.path.join(d, f"rc{r}")).read()
+
+
+def test_comm_runtime_reports_a_missing_rank(tmp_path):
+    """A rank that never shows up is an error after the timeout, not a hang (csrc/comm_runtime.cu: send_msg)."""
+    import ctypes
+    from hetseq_9cme_b200.ops import native
+    if not native.cuda_lib_available():
+        pytest.skip("libb200seq.so not built")
+    lib = native.cuda_lib()
+    lib.b200_comm_selftest.argtypes = [ctypes.c_int, ctypes.c_int, ctypes.c_char_p, ctypes.c_int]
+    rc = lib.b200_comm_selftest(0, 2, f"selftest.alone.{os.getpid()}".encode(), 300)
+    assert rc != 0 and b"cannot reach rank 1" in lib.b200_last_error()

@@ -58,12 +58,19 @@ __device__ __forceinline__ void ln_load_row(const LnCommon<T>& a, int row, int l
   }
 }
 
-template <typename T, int NV>
-__global__ void __launch_bounds__(kLnThreads)
+// PIPE: the rows of a warp stream through shared memory with cp.async, one row ahead: every thread copies the
+// vectors it will itself consume (no barrier needed), so the loads of row i+1 are in flight while row i is being
+// normalised and stored.  Without it all warps of the (single-wave) grid load, then compute, then store in step
+// and the three phases add up: 12.8 us for 4096 x 768 fp32 against 5.8 us of HBM time.
+template <typename T, int NV, bool PIPE>
+__global__ void __launch_bounds__(kLnThreads, PIPE ? 2 : 4)
 ln_fwd_kernel(const LnCommon<T> a, T* __restrict__ y, long long ldy, float* __restrict__ mean_out,
               float* __restrict__ rstd_out) {
   pdl_trigger();
   pdl_wait();
+  using R = typename Raw4<T>::type;
+  extern __shared__ __align__(16) unsigned char ln_pipe_smem[];   // PIPE: R [2 stages][2 tensors][NV][kLnThreads]
+  R* const buf = reinterpret_cast<R*>(ln_pipe_smem);
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const unsigned long long seed = a.seed_dev ? *a.seed_dev : 0ull;
   const Philox ph(seed);
@@ -71,9 +78,55 @@ ln_fwd_kernel(const LnCommon<T> a, T* __restrict__ y, long long ldy, float* __re
   const float ikp = a.p_pre > 0.f ? 1.f / (1.f - a.p_pre) : 1.f;
   const float ikq = a.p_post > 0.f ? 1.f / (1.f - a.p_post) : 1.f;
   const float inv_cols = 1.f / (float)a.cols;
-  for (int row = blockIdx.x * kLnWarps + warp; row < a.rows; row += gridDim.x * kLnWarps) {
-    f4 v[NV], mask[NV];
-    ln_load_row<T, NV>(a, row, lane, ph, thr_pre, ikp, v, mask);
+  const int stride = gridDim.x * kLnWarps;
+  int row = blockIdx.x * kLnWarps + warp;
+  auto issue = [&](int r, int stage) {
+#pragma unroll
+    for (int k = 0; k < NV; ++k) {
+      const int c = (k * 32 + lane) * 4;
+      if (c < a.cols) {
+        cp_async<sizeof(R)>(buf + ((stage * 2 + 0) * NV + k) * kLnThreads + threadIdx.x, a.x + (long long)r * a.ldx + c);
+        if (a.residual)
+          cp_async<sizeof(R)>(buf + ((stage * 2 + 1) * NV + k) * kLnThreads + threadIdx.x, a.residual + (long long)r * a.ldr + c);
+      }
+    }
+  };
+  if constexpr (PIPE) {
+    if (row < a.rows) issue(row, 0);
+    cp_async_commit();
+  }
+  for (int it = 0; row < a.rows; row += stride, ++it) {
+    f4 v[NV];
+    if constexpr (PIPE) {
+      if (row + stride < a.rows) issue(row + stride, (it + 1) & 1);
+      cp_async_commit();                    // one group per iteration (possibly empty): the count below stays uniform
+      cp_async_wait<1>();                   // everything but the newest group has landed: this row is in `it & 1`
+      const int st = it & 1;
+#pragma unroll
+      for (int k = 0; k < NV; ++k) {
+        const int c = (k * 32 + lane) * 4;
+        v[k] = {0.f, 0.f, 0.f, 0.f};
+        if (c < a.cols) {
+          f4 t = Raw4<T>::cvt(buf[((st * 2 + 0) * NV + k) * kLnThreads + threadIdx.x]);
+          if (a.bias) {
+            const f4 b = load4<T>(a.bias + c);
+            t.x += b.x; t.y += b.y; t.z += b.z; t.w += b.w;
+          }
+          if (a.p_pre > 0.f) {
+            const f4 m = dropout_scale4(ph, (unsigned long long)row * a.cols + c, a.stream_pre, thr_pre, ikp);
+            t.x *= m.x; t.y *= m.y; t.z *= m.z; t.w *= m.w;
+          }
+          if (a.residual) {
+            const f4 r = Raw4<T>::cvt(buf[((st * 2 + 1) * NV + k) * kLnThreads + threadIdx.x]);
+            t.x += r.x; t.y += r.y; t.z += r.z; t.w += r.w;
+          }
+          v[k] = t;
+        }
+      }
+    } else {
+      f4 mask[NV];
+      ln_load_row<T, NV>(a, row, lane, ph, thr_pre, ikp, v, mask);
+    }
     float s = 0.f;
 #pragma unroll
     for (int k = 0; k < NV; ++k) s += v[k].x + v[k].y + v[k].z + v[k].w;
@@ -205,15 +258,19 @@ struct LnDirect {
 // of spills per thread but half as many warps again to hide the load -> reduce -> store chain behind.  Measured on the
 // BERT-base step (B200, 30 steps, twice each): 7.670 ms with 2, 7.712 ms with 3 — the spills cost more than the extra
 // warps hide — so 2 is the default and B200_LN_BWD_OCC=3 selects the other instantiation.
-template <typename T, int NVH, int OCC>
+// PIPE: as in the forward kernel, x / residual / dy of the NEXT group of four rows are copied to shared memory with
+// cp.async (each thread its own vectors) while the current group is reduced and stored.
+template <typename T, int NVH, int OCC, bool PIPE>
 __global__ void __launch_bounds__(kLnThreads, OCC)
 ln_bwd2_kernel(const LnCommon<T> a, const T* __restrict__ dy, long long lddy, const float* __restrict__ mean_in,
                const float* __restrict__ rstd_in, T* __restrict__ ds, long long ldds, T* __restrict__ dz, long long lddz,
                float* __restrict__ scratch, int want_dbias, const LnDirect direct) {
   pdl_trigger();
   pdl_wait();
-  extern __shared__ float red[];            // [4 row-slots][cols] for the final fold
+  extern __shared__ float red[];            // [4 row-slots][cols] for the final fold; PIPE: then R [2][3][NVH][kLnThreads]
   __shared__ float2 part[2][4][2];          // [parity][row slot][half]
+  using R = typename Raw4<T>::type;
+  R* const buf = reinterpret_cast<R*>(red + 4 * a.cols);
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int slot = warp >> 1, half = warp & 1;
   const unsigned long long seed = a.seed_dev ? *a.seed_dev : 0ull;
@@ -227,20 +284,42 @@ ln_bwd2_kernel(const LnCommon<T> a, const T* __restrict__ dy, long long lddy, co
 #pragma unroll
   for (int k = 0; k < NVH; ++k) acc_g[k] = acc_b[k] = acc_bias[k] = {0.f, 0.f, 0.f, 0.f};
 
+  auto issue = [&](int r, int stage) {
+#pragma unroll
+    for (int k = 0; k < NVH; ++k) {
+      const int c = cbase + (k * 32 + lane) * 4;
+      cp_async<sizeof(R)>(buf + ((stage * 3 + 0) * NVH + k) * kLnThreads + threadIdx.x, a.x + (long long)r * a.ldx + c);
+      if (a.residual)
+        cp_async<sizeof(R)>(buf + ((stage * 3 + 1) * NVH + k) * kLnThreads + threadIdx.x, a.residual + (long long)r * a.ldr + c);
+      cp_async<sizeof(R)>(buf + ((stage * 3 + 2) * NVH + k) * kLnThreads + threadIdx.x, dy + (long long)r * lddy + c);
+    }
+  };
+  const int step = gridDim.x * 4;
+  if constexpr (PIPE) {
+    if (blockIdx.x * 4 + slot < a.rows) issue(blockIdx.x * 4 + slot, 0);
+    cp_async_commit();
+  }
   int it = 0;
-  for (int base = blockIdx.x * 4; base < a.rows; base += gridDim.x * 4, ++it) {
+  for (int base = blockIdx.x * 4; base < a.rows; base += step, ++it) {
     const int row = base + slot;
     const bool live = row < a.rows;
     f4 v[NVH], g[NVH];
     uint32_t mbits = 0xFFFFFFFFu;            // pre-dropout keep bits, 4 per vector
     float s1 = 0.f, s2 = 0.f, mean = 0.f, rstd = 0.f;
+    if constexpr (PIPE) {
+      if (row + step < a.rows) issue(row + step, (it + 1) & 1);
+      cp_async_commit();                     // one group per iteration, empty or not
+      cp_async_wait<1>();
+    }
+    const int st = it & 1;
     if (live) {
       mean = mean_in[row];
       rstd = rstd_in[row];
 #pragma unroll
       for (int k = 0; k < NVH; ++k) {
         const int c = cbase + (k * 32 + lane) * 4;
-        f4 t = load4<T>(a.x + (long long)row * a.ldx + c);
+        f4 t = PIPE ? Raw4<T>::cvt(buf[((st * 3 + 0) * NVH + k) * kLnThreads + threadIdx.x])
+                    : load4<T>(a.x + (long long)row * a.ldx + c);
         if (a.bias) {
           const f4 b = load4<T>(a.bias + c);
           t.x += b.x; t.y += b.y; t.z += b.z; t.w += b.w;
@@ -252,10 +331,12 @@ ln_bwd2_kernel(const LnCommon<T> a, const T* __restrict__ dy, long long lddy, co
           mbits = (mbits & ~(0xFu << (4 * k))) | (bits << (4 * k));
         }
         if (a.residual) {
-          const f4 r = load4<T>(a.residual + (long long)row * a.ldr + c);
+          const f4 r = PIPE ? Raw4<T>::cvt(buf[((st * 3 + 1) * NVH + k) * kLnThreads + threadIdx.x])
+                            : load4<T>(a.residual + (long long)row * a.ldr + c);
           t.x += r.x; t.y += r.y; t.z += r.z; t.w += r.w;
         }
-        f4 d = load4<T>(dy + (long long)row * lddy + c);
+        f4 d = PIPE ? Raw4<T>::cvt(buf[((st * 3 + 2) * NVH + k) * kLnThreads + threadIdx.x])
+                    : load4<T>(dy + (long long)row * lddy + c);
         if (a.p_post > 0.f) {
           const f4 m = dropout_scale4(ph, (unsigned long long)row * a.cols + c, a.stream_post, thr_post, ikq);
           d.x *= m.x; d.y *= m.y; d.z *= m.z; d.w *= m.w;
@@ -361,17 +442,59 @@ static int check_ln(const b200_ln_args* a) {
   return 0;
 }
 
+// Streaming (cp.async) variants: bit 0 = forward, bit 1 = backward, -1 = automatic; CTAs per SM of each (the grid is that
+// many times the SM count, so a warp owns several rows and the prefetch has something to run ahead of).
+// B200_LN_PIPE / B200_LN_PIPE_FWD_CTAS / B200_LN_PIPE_BWD_CTAS set the start-up values, b200_ln_config changes them
+// at run time.  Measured on B200 (tools/gpu_probe_ln.py, 4096 rows, dropout + bias + residual, us per call):
+//   fp32 x 768:   forward 11.8 direct / 13.7 streaming;  backward 19.5 direct / 15.6 streaming (18.7 with 1 CTA/SM)
+//   bf16 x 1024:  forward 15.1 / 14.4;                    backward 15.8 / 16.5
+// and in the BERT-base TF32 step 7.765 -> 7.659 ms with the streaming backward only (7.82 with both).  The forward
+// kernel already keeps 28 warps per SM in flight and gains nothing; the backward kernel is held to 16 warps by its
+// registers and gains the memory-level parallelism it lacks.  Automatic = streaming backward for fp32 storage.
+struct LnConfig {
+  int pipe, fwd_ctas, bwd_ctas;
+};
+static LnConfig& ln_config() {
+  static LnConfig c = [] {
+    auto geti = [](const char* n, int d) { const char* e = getenv(n); return e && e[0] ? atoi(e) : d; };
+    return LnConfig{geti("B200_LN_PIPE", -1), geti("B200_LN_PIPE_FWD_CTAS", 2), geti("B200_LN_PIPE_BWD_CTAS", 2)};
+  }();
+  return c;
+}
+
+template <typename K>
+static int ln_allow_smem(K kernel, size_t bytes) {
+  // 40 KB: the kernels also hold a little static shared memory, and the 48 KB default limit covers both
+  if (bytes > 40 * 1024) B200_CUDA(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes));
+  return 0;
+}
+
+template <typename T, int NV>
+static int ln_fwd_launch(const b200_ln_args* a, const LnCommon<T>& c, cudaStream_t st) {
+  const LnConfig cfg = ln_config();
+  int blocks = (a->rows + kLnWarps - 1) / kLnWarps;
+  const size_t pipe_smem = (size_t)2 * 2 * NV * kLnThreads * sizeof(typename Raw4<T>::type);
+  if (cfg.pipe > 0 && (cfg.pipe & 1) && blocks > num_sms()) {   // fewer rows than warps of one wave: nothing to run ahead of
+    const int ctas = cfg.fwd_ctas < 1 ? 1 : (cfg.fwd_ctas > 2 ? 2 : cfg.fwd_ctas);
+    if (blocks > num_sms() * ctas) blocks = num_sms() * ctas;
+    if (int rc = ln_allow_smem(ln_fwd_kernel<T, NV, true>, pipe_smem)) return rc;
+    B200_CUDA(launch_pdl(ln_fwd_kernel<T, NV, true>, dim3(blocks), dim3(kLnThreads), pipe_smem, st, 1, c, (T*)a->y, a->ldy, a->mean, a->rstd));
+    B200_LAUNCHED("ln_fwd_kernel<pipe>");
+    return 0;
+  }
+  const int cap = num_sms() * 8;
+  if (blocks > cap) blocks = cap;
+  B200_CUDA(launch_pdl(ln_fwd_kernel<T, NV, false>, dim3(blocks), dim3(kLnThreads), 0, st, 1, c, (T*)a->y, a->ldy, a->mean, a->rstd));
+  B200_LAUNCHED("ln_fwd_kernel");
+  return 0;
+}
+
 template <typename T>
 static int ln_fwd_t(const b200_ln_args* a, cudaStream_t st) {
   const LnCommon<T> c = make_common<T>(a);
-  int blocks = (a->rows + kLnWarps - 1) / kLnWarps;
-  const int cap = num_sms() * 8;
-  if (blocks > cap) blocks = cap;
-  if (a->cols <= 256) launch_pdl(ln_fwd_kernel<T, 2>, dim3(blocks), dim3(kLnThreads), 0, st, 1, c, (T*)a->y, a->ldy, a->mean, a->rstd);
-  else if (a->cols <= 768) launch_pdl(ln_fwd_kernel<T, 6>, dim3(blocks), dim3(kLnThreads), 0, st, 1, c, (T*)a->y, a->ldy, a->mean, a->rstd);
-  else launch_pdl(ln_fwd_kernel<T, 8>, dim3(blocks), dim3(kLnThreads), 0, st, 1, c, (T*)a->y, a->ldy, a->mean, a->rstd);
-  B200_LAUNCHED("ln_fwd_kernel");
-  return 0;
+  if (a->cols <= 256) return ln_fwd_launch<T, 2>(a, c, st);
+  if (a->cols <= 768) return ln_fwd_launch<T, 6>(a, c, st);
+  return ln_fwd_launch<T, 8>(a, c, st);
 }
 
 static int ln_bwd_blocks(int rows) {
@@ -386,22 +509,29 @@ static int ln_bwd_t(const b200_ln_args* a, cudaStream_t st) {
   if ((a->cols & 255) == 0) {
     // two warps per row
     static const int occ = [] { const char* e = getenv("B200_LN_BWD_OCC"); const int v = e ? atoi(e) : 2; return v == 3 ? 3 : 2; }();
+    const LnConfig cfg = ln_config();
     int blocks = (a->rows + 3) / 4;
-    const int cap = occ == 2 ? kLnBwdMaxBlocks : kLnBwdMaxBlocks3;
+    const bool pipe = (cfg.pipe < 0 ? sizeof(T) == 4 : (cfg.pipe & 2) != 0) && blocks > num_sms();
+    int cap = occ == 2 ? kLnBwdMaxBlocks : kLnBwdMaxBlocks3;
+    if (pipe) cap = num_sms() * (cfg.bwd_ctas < 1 ? 1 : (cfg.bwd_ctas > 2 ? 2 : cfg.bwd_ctas));
     if (blocks > cap) blocks = cap;
     if (blocks < 1) blocks = 1;
     const size_t smem2 = (size_t)4 * a->cols * sizeof(float);
     const int want = a->dbias != nullptr;
     const bool direct_mode = a->scratch == nullptr;
     const LnDirect direct{a->dgamma, a->dbeta, a->dbias};
+#define LN_BWD2_GO(KERN, SMEM)                                                                                        \
+  do {                                                                                                                \
+    if (int rc = ln_allow_smem(KERN, SMEM)) return rc;                                                                \
+    B200_CUDA(launch_pdl(KERN, dim3(blocks), dim3(kLnThreads), SMEM, st, 1, c, (const T*)a->dy, a->lddy, a->mean,     \
+                         a->rstd, (T*)a->ds, a->ldds, (T*)a->dz, a->lddz, (float*)a->scratch, want, direct));         \
+  } while (0)
 #define LN_BWD2(NVH)                                                                                                  \
   do {                                                                                                                \
-    if (occ == 2)                                                                                                     \
-      launch_pdl(ln_bwd2_kernel<T, NVH, 2>, dim3(blocks), dim3(kLnThreads), smem2, st, 1, c, (const T*)a->dy, a->lddy, \
-                 a->mean, a->rstd, (T*)a->ds, a->ldds, (T*)a->dz, a->lddz, (float*)a->scratch, want, direct);         \
-    else                                                                                                              \
-      launch_pdl(ln_bwd2_kernel<T, NVH, 3>, dim3(blocks), dim3(kLnThreads), smem2, st, 1, c, (const T*)a->dy, a->lddy, \
-                 a->mean, a->rstd, (T*)a->ds, a->ldds, (T*)a->dz, a->lddz, (float*)a->scratch, want, direct);         \
+    const size_t pipe_smem = smem2 + (size_t)2 * 3 * NVH * kLnThreads * sizeof(typename Raw4<T>::type);               \
+    if (pipe) LN_BWD2_GO((ln_bwd2_kernel<T, NVH, 2, true>), pipe_smem);                                               \
+    else if (occ == 2) LN_BWD2_GO((ln_bwd2_kernel<T, NVH, 2, false>), smem2);                                         \
+    else LN_BWD2_GO((ln_bwd2_kernel<T, NVH, 3, false>), smem2);                                                       \
   } while (0)
     switch (a->cols / 256) {
       case 1: LN_BWD2(1); break;
@@ -410,7 +540,8 @@ static int ln_bwd_t(const b200_ln_args* a, cudaStream_t st) {
       default: LN_BWD2(4); break;
     }
 #undef LN_BWD2
-    B200_LAUNCHED("ln_bwd2_kernel");
+#undef LN_BWD2_GO
+    B200_LAUNCHED(pipe ? "ln_bwd2_kernel<pipe>" : "ln_bwd2_kernel");
     if (direct_mode) return 0;
     dim3 grid2((a->cols + 31) / 32, 3);
     ln_bwd_finalize<<<grid2, 256, 0, st>>>((const float*)a->scratch, blocks, a->cols, a->dgamma, a->dbeta, a->dbias);
@@ -439,6 +570,18 @@ static int ln_bwd_t(const b200_ln_args* a, cudaStream_t st) {
 using namespace b200;
 
 extern "C" long long b200_ln_bwd_scratch_bytes(int cols) { return (long long)kLnBwdMaxBlocks3 * 3 * cols * 4; }
+
+// Select the streaming (cp.async) LayerNorm kernels at run time: pipe bit 0 = forward, bit 1 = backward; *_ctas = CTAs
+// per SM of their grids (1 or 2).  pipe = -1 selects the automatic choice, pipe < -1 / ctas <= 0 leave a field as it
+// is.  Not thread-safe against running launches.
+extern "C" int b200_ln_config(int pipe, int fwd_ctas, int bwd_ctas) {
+  LnConfig& c = ln_config();
+  if (pipe >= 0) c.pipe = pipe & 3;
+  else if (pipe == -1) c.pipe = -1;
+  if (fwd_ctas > 0) c.fwd_ctas = fwd_ctas;
+  if (bwd_ctas > 0) c.bwd_ctas = bwd_ctas;
+  return c.pipe;
+}
 
 extern "C" int b200_ln_fwd(const b200_ln_args* a, void* stream) {
   int rc = check_ln(a);

@@ -58,6 +58,37 @@ __device__ __forceinline__ void store1<float>(float* p, float v) { *p = v; }
 template <>
 __device__ __forceinline__ void store1<__nv_bfloat16>(__nv_bfloat16* p, float v) { *p = __float2bfloat16_rn(v); }
 
+// ---- cp.async (LDGSTS): per-thread asynchronous global -> shared copies, completion tracked per thread in commit
+// groups.  A thread that only reads back what it copied itself needs no barrier: wait_group makes its own copies
+// visible to it.  Used as a register-free prefetch buffer by the streaming LayerNorm kernels.
+template <int BYTES>
+__device__ __forceinline__ void cp_async(void* smem_dst, const void* gsrc) {
+  const uint32_t d = (uint32_t)__cvta_generic_to_shared(smem_dst);
+  if constexpr (BYTES == 16) {
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(d), "l"(gsrc) : "memory");
+  } else {
+    asm volatile("cp.async.ca.shared.global [%0], [%1], %2;" ::"r"(d), "l"(gsrc), "n"(BYTES) : "memory");
+  }
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
+
+// storage form of four consecutive elements (what load4 reads) and its conversion to registers
+template <typename T> struct Raw4;
+template <> struct Raw4<float> {
+  using type = float4;
+  static __device__ __forceinline__ f4 cvt(const float4& v) { return {v.x, v.y, v.z, v.w}; }
+};
+template <> struct Raw4<__nv_bfloat16> {
+  using type = uint2;
+  static __device__ __forceinline__ f4 cvt(const uint2& u) {
+    const __nv_bfloat162 a = *reinterpret_cast<const __nv_bfloat162*>(&u.x);
+    const __nv_bfloat162 b = *reinterpret_cast<const __nv_bfloat162*>(&u.y);
+    return {__low2float(a), __high2float(a), __low2float(b), __high2float(b)};
+  }
+};
+
 __device__ __forceinline__ float warp_sum(float v) {
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);

@@ -263,6 +263,13 @@ def ln_fwd(x, gamma, beta, *, bias=None, residual=None, eps=1e-12, p_pre=0.0, p_
     return y, mean, rstd
 
 
+def ln_config(pipe: int = -2, fwd_ctas: int = 0, bwd_ctas: int = 0) -> int:
+    """Select the streaming (cp.async) LayerNorm kernels: ``pipe`` bit 0 = forward, bit 1 = backward, -1 = automatic
+    (streaming backward for fp32 storage); ``*_ctas`` = CTAs per SM of their grids.  Defaults leave a field unchanged;
+    returns the mode in effect (csrc/norm_kernels.cu)."""
+    return int(_lib().b200_ln_config(int(pipe), int(fwd_ctas), int(bwd_ctas)))
+
+
 def ln_bwd(dy, x, gamma, beta, mean, rstd, dgamma, dbeta, *, bias=None, dbias=None, residual=None, eps=1e-12, p_pre=0.0,
            p_post=0.0, seed=None, stream_pre=0, stream_post=0, want_ds=True, want_dz=False, ws: Optional[Workspace] = None,
            deterministic: bool = False):

@@ -149,6 +149,10 @@ typedef struct {
 long long b200_ln_bwd_scratch_bytes(int cols);
 int b200_ln_fwd(const b200_ln_args* a, void* stream);
 int b200_ln_bwd(const b200_ln_args* a, void* stream);
+/* Streaming (cp.async) LayerNorm kernels: pipe bit 0 = forward, bit 1 = backward; *_ctas = CTAs per SM of their
+ * grids (1 or 2).  pipe = -1: automatic (streaming backward for fp32 storage); pipe < -1 / ctas <= 0 leave the field
+ * unchanged.  Returns the mode in effect.  Start-up values: B200_LN_PIPE, B200_LN_PIPE_FWD_CTAS, B200_LN_PIPE_BWD_CTAS. */
+int b200_ln_config(int pipe, int fwd_ctas, int bwd_ctas);
 
 /* ------------------------------------------------------------------------------------------------
  * Embeddings, masked-row compaction, cross-entropy, tiny-N heads, column sums.

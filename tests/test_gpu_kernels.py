@@ -123,6 +123,49 @@ def test_layernorm_fwd_bwd(K, dtype, cols):
     assert _rel(dbias, xr.grad.sum(0)) < tol
 
 
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+@pytest.mark.parametrize("cols,ctas", [(768, 2), (768, 1), (1024, 2), (256, 2)])
+def test_layernorm_streaming_kernels_match(K, dtype, cols, ctas):
+    """The cp.async-pipelined LayerNorm kernels (b200_ln_config) run the same arithmetic on the same values as the
+    direct-load ones: y / mean / rstd / ds / dz bit for bit (pre-dropout on, ragged row count, several rows per
+    warp), parameter gradients up to the order of the atomic adds."""
+    torch.manual_seed(11)
+    rows, p = 4099, 0.1
+    ws = K.Workspace.get("cuda")
+    ws.set_seed(77)
+    x = torch.randn(rows, cols, device="cuda").to(dtype)
+    res = torch.randn(rows, cols, device="cuda").to(dtype)
+    bias = torch.randn(cols, device="cuda").to(dtype)
+    gamma = (torch.rand(cols, device="cuda") + 0.5).to(dtype)
+    beta = torch.randn(cols, device="cuda").to(dtype)
+    dy = torch.randn(rows, cols, device="cuda").to(dtype)
+
+    def run():
+        y, mean, rstd = K.ln_fwd(x, gamma, beta, bias=bias, residual=res, p_pre=p, seed=ws.seed, stream_pre=9)
+        dg, db, dbias = (torch.zeros(cols, device="cuda") for _ in range(3))
+        ds, dz = K.ln_bwd(dy, x, gamma, beta, mean, rstd, dg, db, bias=bias, dbias=dbias, residual=res, p_pre=p,
+                          seed=ws.seed, stream_pre=9, want_dz=True)
+        dg2, db2, dbias2 = (torch.zeros(cols, device="cuda") for _ in range(3))
+        K.ln_bwd(dy, x, gamma, beta, mean, rstd, dg2, db2, bias=bias, dbias=dbias2, residual=res, p_pre=p,
+                 seed=ws.seed, stream_pre=9, want_dz=True, deterministic=True)
+        torch.cuda.synchronize()
+        return (y, mean, rstd, ds, dz), (dg, db, dbias, dg2, db2, dbias2)
+
+    before = K.ln_config()
+    try:
+        K.ln_config(0)
+        exact0, sums0 = run()
+        assert K.ln_config(3, ctas, ctas) == 3
+        exact1, sums1 = run()
+    finally:
+        K.ln_config(before, 2, 2)
+    for a, b in zip(exact0, exact1):
+        assert torch.equal(a, b)
+    for a, b in zip(sums0, sums1):
+        assert _rel(b, a) < 1e-5
+    assert 0.05 < (exact1[4] == 0).float().mean().item() < 0.15      # dz carries the pre-dropout mask
+
+
 def test_layernorm_dropout_is_consistent(K):
     """Forward and backward must regenerate the same mask; keep-rate must match p."""
     torch.manual_seed(4)

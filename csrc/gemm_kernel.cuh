@@ -36,7 +36,6 @@ struct GemmArgs {
   const unsigned long long* seed_dev;
   unsigned long long stream_id;
   long long ldp;                 // row pitch of the probability tensors (dropout element index)
-  int a_box, b_box;              // rows per TMA box of a K-major A / B tile (divide 128 / the CTA's B rows)
 };
 
 constexpr int kBM = 128;
@@ -178,13 +177,13 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
             if (crank == 0) mbar_arrive_expect_tx(&full_bar[s], 2 * STAGE_BYTES);
             const uint32_t fb = mapa_u32(smem_u32(&full_bar[s]), 0);
             if constexpr (!A_MN) {
-              for (int r = 0; r < kBM; r += args.a_box) tma_load_4d_2sm(sA + r * 128, &tmA, fb, k0, m0 + r, b0, b1);
+              tma_load_4d_2sm(sA, &tmA, fb, k0, m0, b0, b1);
             } else {
 #pragma unroll
               for (int sl = 0; sl < kBM / EA; ++sl) tma_load_4d_2sm(sA + sl * SLAB_BYTES, &tmA, fb, m0 + sl * EA, k0, b0, b1);
             }
             if constexpr (!B_MN) {
-              for (int r = 0; r < B_ROWS; r += args.b_box) tma_load_4d_2sm(sB + r * 128, &tmB, fb, k0, n0 + r, b0, b1);
+              tma_load_4d_2sm(sB, &tmB, fb, k0, n0, b0, b1);
             } else {
 #pragma unroll
               for (int sl = 0; sl < B_ROWS / EA; ++sl) tma_load_4d_2sm(sB + sl * SLAB_BYTES, &tmB, fb, n0 + sl * EA, k0, b0, b1);
@@ -192,13 +191,13 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
           } else {
             mbar_arrive_expect_tx(&full_bar[s], STAGE_BYTES);
             if constexpr (!A_MN) {
-              for (int r = 0; r < kBM; r += args.a_box) tma_load_4d(sA + r * 128, &tmA, &full_bar[s], k0, m0 + r, b0, b1);
+              tma_load_4d(sA, &tmA, &full_bar[s], k0, m0, b0, b1);
             } else {
 #pragma unroll
               for (int sl = 0; sl < kBM / EA; ++sl) tma_load_4d(sA + sl * SLAB_BYTES, &tmA, &full_bar[s], m0 + sl * EA, k0, b0, b1);
             }
             if constexpr (!B_MN) {
-              for (int r = 0; r < BN; r += args.b_box) tma_load_4d(sB + r * 128, &tmB, &full_bar[s], k0, n0 + r, b0, b1);
+              tma_load_4d(sB, &tmB, &full_bar[s], k0, n0, b0, b1);
             } else {
 #pragma unroll
               for (int sl = 0; sl < BN / EA; ++sl) tma_load_4d(sB + sl * SLAB_BYTES, &tmB, &full_bar[s], n0 + sl * EA, k0, b0, b1);

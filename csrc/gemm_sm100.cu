@@ -221,22 +221,10 @@ static int gemm_impl(const b200_gemm_desc* d, cudaStream_t stream) {
 
   CUtensorMap tA, tB, tD, tD2;
   int rc;
-  // rows per TMA box of the K-major operand tiles.  B200_GEMM_BOX = 64 / 128 splits a tile's load into several TMA
-  // operations (the swizzle pattern repeats every 8 rows, so sub-boxes land exactly where the single box would)
-  const int b_rows = cta2 ? bn / 2 : bn;
-  int a_box = kBM, b_box = b_rows;
-  {
-    const char* e = getenv("B200_GEMM_BOX");
-    const int v = e ? atoi(e) : 0;
-    if (v == 64 || v == 128) {
-      if (kBM % v == 0) a_box = v;
-      if (b_rows % v == 0) b_box = v;
-    }
-  }
-  if (!d->a_mn) rc = make_tmap_4d(&tA, d->A, es, in_bf16, d->M, d->K, d->lda, BK, a_box, false, nb0, d->sa0, nb1, d->sa1);
+  if (!d->a_mn) rc = make_tmap_4d(&tA, d->A, es, in_bf16, d->M, d->K, d->lda, BK, kBM, false, nb0, d->sa0, nb1, d->sa1);
   else rc = make_tmap_4d(&tA, d->A, es, in_bf16, d->K, d->M, d->lda, EA, BK, es == 4, nb0, d->sa0, nb1, d->sa1);
   if (rc) return rc;
-  if (!d->b_mn) rc = make_tmap_4d(&tB, d->B, es, in_bf16, d->N, d->K, d->ldb, BK, b_box, false, nb0, d->sb0, nb1, d->sb1);
+  if (!d->b_mn) rc = make_tmap_4d(&tB, d->B, es, in_bf16, d->N, d->K, d->ldb, BK, cta2 ? bn / 2 : bn, false, nb0, d->sb0, nb1, d->sb1);
   else rc = make_tmap_4d(&tB, d->B, es, in_bf16, d->K, d->N, d->ldb, EA, BK, es == 4, nb0, d->sb0, nb1, d->sb1);
   if (rc) return rc;
   const int CW = 128 / os;
@@ -277,8 +265,6 @@ static int gemm_impl(const b200_gemm_desc* d, cudaStream_t stream) {
   a.seed_dev = d->seed_dev;
   a.stream_id = d->stream_id;
   a.ldp = d->ldd;
-  a.a_box = a_box;
-  a.b_box = b_box;
   if (epi_mode != 0) a.aux_mode = B200_AUX_NONE;     // aux is consumed by the softmax-backward epilogue itself
 
   switch (d->dtype) {

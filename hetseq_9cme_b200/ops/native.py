@@ -57,6 +57,10 @@ class GemmDesc(ctypes.Structure):
 
 
 def lib_path(name: str = "libb200seq.so") -> Path:
+    # B200SEQ_LIB: load another build of the CUDA library (A/B runs against an older build of the kernels)
+    override = os.environ.get("B200SEQ_LIB")
+    if override and name == "libb200seq.so":
+        return Path(override)
     return _LIB_DIR / name
 
 

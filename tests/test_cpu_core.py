@@ -342,3 +342,40 @@ def test_reference_style_checkpoint_with_empty_extra_state_loads(tmp_path):
     assert extra == {}
     for (k, a), (_, b) in zip(c.get_model().state_dict().items(), net.state_dict().items()):
         assert torch.equal(a, b), k
+
+
+def test_public_api_surface_of_the_reference_is_present():
+    """Every module / class / function name a HetSeq user imports (taken from the reference's
+    `hetseq/` tree) exists under the same name here."""
+    import importlib
+    surface = {
+        "train": "cli_main distributed_main main train get_training_stats",
+        "options": "get_training_parser add_dataset_args add_distributed_training_args add_optimization_args "
+                   "add_checkpoint_args eval_str_list eval_bool parse_args_and_arch",
+        "controller": "Controller",
+        "distributed_utils": "distributed_init is_master suppress_output get_rank get_world_size get_default_group "
+                             "all_reduce all_gather_list",
+        "checkpoint_utils": "save_checkpoint load_checkpoint load_checkpoint_to_cpu checkpoint_paths torch_persistent_save "
+                            "convert_state_dict_type save_state verify_checkpoint_directory",
+        "optim": "_Optimizer _Adam _Adadelta Adam Adadelta",
+        "lr_scheduler": "_LRScheduler PolynomialDecayScheduler",
+        "meters": "AverageMeter TimeMeter StopwatchMeter",
+        "progress_bar": "build_progress_bar progress_bar noop_progress_bar simple_progress_bar format_stat",
+        "tasks": "Task LanguageModelingTask MNISTTask MNISTNet BertForTokenClassificationTask BertForELClassificationTask",
+        "data": "BertH5pyData ConBertH5pyData MNISTDataset BertNerDataset BertELDataset",
+        "data.data_utils": "numpy_seed batch_by_size",
+        "data.iterators": "CountingIterator EpochBatchIterator GroupedIterator ShardedIterator",
+        "data_collator": "YD_DataCollatorForTokenClassification YD_DataCollatorForELClassification",
+        "bert_modeling": "BertConfig BertLayerNorm LinearActivation BertModel BertForPreTraining BertForMaskedLM "
+                         "BertForNextSentencePrediction BertForSequenceClassification BertForMultipleChoice "
+                         "BertForTokenClassification BertForQuestionAnswering",
+        "model": "BertForELClassification",
+        "eval_mnist": "main",
+        "eval_bert_fine_tuning_ner": "main",
+    }
+    missing = []
+    for mod, names in surface.items():
+        m = importlib.import_module("hetseq_9cme_b200." + mod)
+        missing += ["%s.%s" % (mod, n) for n in names.split() if not hasattr(m, n)]
+    assert not missing, missing
+    assert hasattr(importlib.import_module("hetseq_9cme_b200.controller").Controller, "valid_step")

@@ -225,6 +225,9 @@ _ENGINE = [
     (("--profile",), dict(action="store_true", help="emit NVTX ranges per phase")),
     (("--log-jsonl",), dict(type=str, default=None, metavar="PATH", help="also append per-step stats as JSON lines")),
     (("--fault-inject",), dict(type=str, default=None, metavar="RANK:STEP", help="testing: kill RANK at STEP")),
+    (("--max-restarts",), dict(type=int, default=0, metavar="N",
+                               help="when a rank of this node dies, stop the others and start all of them again from "
+                                    "checkpoint_last.pt, at most N times (use with --save-interval-updates)")),
 ]
 
 

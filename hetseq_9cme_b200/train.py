@@ -14,7 +14,9 @@ import math
 import os
 import sys
 
-if __name__ == "__main__" and __package__ is None:  # allow `python hetseq_9cme_b200/train.py`
+# allow `python hetseq_9cme_b200/train.py` — also in the children torch.multiprocessing.spawn starts, which import this
+# file again as "__mp_main__"
+if __name__ in ("__main__", "__mp_main__") and not __package__:
     sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
     __package__ = "hetseq_9cme_b200"
 
@@ -31,7 +33,8 @@ def _maybe_fault_inject(args, num_updates):
     spec = getattr(args, "fault_inject", None) or os.environ.get("HETSEQ_FAULT_INJECT")
     if spec:
         rank, step = (int(x) for x in spec.split(":"))
-        if rank == getattr(args, "distributed_rank", 0) and num_updates == step:
+        # only in the first attempt: a restarted run passes the same update count again
+        if rank == getattr(args, "distributed_rank", 0) and num_updates == step and not getattr(args, "restart_attempt", 0):
             distributed_utils.log_all("| fault injection: rank {} exits at update {}".format(rank, step))
             os._exit(17)
 
@@ -211,6 +214,31 @@ def distributed_main(i, args, start_rank=0):
     main(args, init_distributed=True)
 
 
+def _spawn_supervised(args, nprocs, spawn_args, fresh_port=False):
+    """``torch.multiprocessing.spawn`` with failure recovery (``--max-restarts``): when a rank dies, spawn stops its
+    siblings and raises; all ranks of this node are then started again and resume from ``checkpoint_last.pt`` (the
+    checkpoint carries the iterator position, the schedule and the update count, so the run continues where the last
+    checkpoint left it).  The reference has no recovery path: a dead rank hangs the job until the scheduler kills it.
+    On several nodes every node's launcher sees its own ranks fail (collective error, or the peer-to-peer watchdog,
+    exit code 86) and restarts them; they meet again at the same ``--distributed-init-method``."""
+    from torch.multiprocessing import ProcessExitedException, ProcessRaisedException
+    attempt = 0
+    while True:
+        args.restart_attempt = attempt
+        if fresh_port:
+            args.distributed_init_method = "tcp://127.0.0.1:{}".format(distributed_utils.find_free_port())
+        try:
+            torch.multiprocessing.spawn(fn=distributed_main, args=spawn_args, nprocs=nprocs)
+            return
+        except (ProcessExitedException, ProcessRaisedException) as e:
+            if attempt >= int(getattr(args, "max_restarts", 0) or 0):
+                raise
+            attempt += 1
+            first = str(e).strip().splitlines()[0] if str(e).strip() else type(e).__name__
+            print("| a rank failed ({}); restart {}/{} from the last checkpoint".format(first, attempt, args.max_restarts),
+                  flush=True)
+
+
 def cli_main(argv=None):
     args = options.parse_training_args(argv)
     ndev = torch.cuda.device_count() if (torch.cuda.is_available() and not args.cpu) else 0
@@ -220,15 +248,14 @@ def cli_main(argv=None):
         if args.distributed_gpus > 1 and not args.distributed_no_spawn:
             start_rank = args.distributed_rank
             args.distributed_rank = None
-            torch.multiprocessing.spawn(fn=distributed_main, args=(args, start_rank), nprocs=args.distributed_gpus)
+            _spawn_supervised(args, args.distributed_gpus, (args, start_rank))
         else:
             distributed_main(args.device_id, args)
     elif args.distributed_world_size > 1:
         if ndev:
             assert args.distributed_world_size <= ndev, "--distributed-world-size exceeds the visible GPUs"
-        args.distributed_init_method = "tcp://127.0.0.1:{}".format(distributed_utils.find_free_port())
         args.distributed_rank = None
-        torch.multiprocessing.spawn(fn=distributed_main, args=(args,), nprocs=args.distributed_world_size)
+        _spawn_supervised(args, args.distributed_world_size, (args,), fresh_port=True)
     else:
         main(args)
 

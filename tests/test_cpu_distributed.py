@@ -110,3 +110,33 @@ def test_comm_runtime_reports_a_missing_rank(tmp_path):
     lib.b200_comm_selftest.argtypes = [ctypes.c_int, ctypes.c_int, ctypes.c_char_p, ctypes.c_int]
     rc = lib.b200_comm_selftest(0, 2, f"selftest.alone.{os.getpid()}".encode(), 300)
     assert rc != 0 and b"cannot reach rank 1" in lib.b200_last_error()
+
+
+def test_dead_rank_is_restarted_from_the_last_checkpoint(tmp_path):
+    """--max-restarts: rank 1 is killed at update 5 (--fault-inject); the launcher stops rank 0, starts both again, they
+    resume from the checkpoint written at update 4 and finish the epoch with the same number of updates as a run
+    without the fault (recovery path the reference does not have: hetseq/train.py:196-250 just spawns)."""
+    import subprocess
+    from hetseq_9cme_b200.data import synthetic
+    d = str(tmp_path)
+    synthetic.make_mnist(d, 16 * 16, 32)        # 16 batches over 2 ranks -> 8 updates
+    save = os.path.join(d, "ckpt")
+    cmd = [sys.executable, os.path.join(ROOT, "hetseq_9cme_b200", "train.py"), "--task", "mnist", "--optimizer", "adadelta",
+           "--data", d, "--cpu", "--distributed-backend", "gloo", "--distributed-world-size", "2", "--max-sentences", "16",
+           "--lr", "1.0", "--valid-subset", "test", "--save-dir", save, "--num-workers", "0", "--clip-norm", "100",
+           "--log-format", "simple", "--log-interval", "1", "--max-epoch", "1", "--seed", "3", "--fast-stat-sync",
+           "--save-interval-updates", "2", "--fault-inject", "1:5", "--max-restarts", "1"]
+    r = subprocess.run(cmd, capture_output=True, text=True, timeout=600, cwd=ROOT)
+    out = r.stdout + r.stderr
+    assert r.returncode == 0, out[-3000:]
+    assert "fault injection: rank 1 exits at update 5" in out
+    assert "restart 1/1 from the last checkpoint" in out
+    assert "loaded checkpoint" in out and "@ 4 updates" in out          # resumed from the mid-epoch checkpoint
+    last = torch.load(os.path.join(save, "checkpoint_last.pt"), map_location="cpu", weights_only=False)
+    assert last["optimizer_history"][-1]["num_updates"] == 8
+    # without --max-restarts the same fault ends the job with an error instead
+    cmd2 = [c for c in cmd]
+    cmd2[cmd2.index("--max-restarts") + 1] = "0"
+    cmd2[cmd2.index("--save-dir") + 1] = os.path.join(d, "ckpt2")
+    r2 = subprocess.run(cmd2, capture_output=True, text=True, timeout=600, cwd=ROOT)
+    assert r2.returncode != 0

@@ -379,3 +379,23 @@ def test_public_api_surface_of_the_reference_is_present():
         missing += ["%s.%s" % (mod, n) for n in names.split() if not hasattr(m, n)]
     assert not missing, missing
     assert hasattr(importlib.import_module("hetseq_9cme_b200.controller").Controller, "valid_step")
+
+
+def test_sharded_step_protocol_has_no_race_in_any_interleaving():
+    """Model check of the cross-rank protocol of the sharded data-parallel step (tools/protocol_model.py: stand-in for
+    a racecheck across processes): every interleaving of 3 ranks x 2 buckets x 2 steps and of 2 ranks x 3
+    buckets x 3 steps is free of stale reads, premature overwrites and deadlocks — and dropping ANY one synchronisation
+    element (the wait for the side stream, the announce-wait of the reduce-scatter or the tail, the tail's 'done
+    reading' round, the completion round of the sharded Adam, the per-bucket wait of the pipelined update) is caught."""
+    sys.path.insert(0, os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "tools"))
+    try:
+        import protocol_model as pm
+    finally:
+        sys.path.pop(0)
+    for pipelined in (False, True):                      # update at the end of the step / --pipelined-update
+        for shape in ((3, 2, 2), (2, 3, 3)):
+            violation, states = pm.check(*shape, pipelined=pipelined)
+            assert violation is None and states > 500, (shape, pipelined, violation, states)
+        for drop in (pm.DROPS_PIPELINED if pipelined else pm.DROPS):
+            violation, _ = pm.check(2, 2, 3, drop=drop, pipelined=pipelined)
+            assert violation is not None, (drop, pipelined)

@@ -399,3 +399,7 @@ def test_sharded_step_protocol_has_no_race_in_any_interleaving():
         for drop in (pm.DROPS_PIPELINED if pipelined else pm.DROPS):
             violation, _ = pm.check(2, 2, 3, drop=drop, pipelined=pipelined)
             assert violation is not None, (drop, pipelined)
+    # inside the one-shot kernel: fine while the whole grid is co-resident, a certain deadlock beyond (hence the
+    # kOneShotMaxBlocks guard in b200_p2p_allreduce)
+    assert pm.check_one_shot(2, 3, 3)[0] is None and pm.check_one_shot(3, 2, 2)[0] is None
+    assert "deadlock" in pm.check_one_shot(2, 4, 3)[0]

@@ -275,6 +275,83 @@ def check(W: int = 2, B: int = 2, T: int = 2, drop: Optional[str] = None, pipeli
     return None, len(seen)
 
 
+
+# ---- inside one kernel: the one-shot all-reduce and the number of co-resident CTAs ------------------------------------
+def check_one_shot(W: int = 2, grid: int = 3, resident: int = 3, epochs: int = 2):
+    """Block-level model of the one-shot kernel (`p2p_allreduce_kernel`, one_shot branch): every CTA waits for the peers'
+    announcement, reads, bumps the per-bucket counter; the CTA that finds the counter at grid-1 resets it, advances the
+    epoch word and signals "done reading"; EVERY CTA then waits for the peers' "done" before it overwrites its part.
+    A CTA occupies one of `resident` slots from its first action until it retires.  Returns (violation or None, states).
+
+    With grid <= resident there is no deadlock in any interleaving; with grid > resident the resident CTAs of every rank
+    wait for a signal that only a not-yet-resident CTA of a peer can cause — the reason `b200_p2p_allreduce` refuses
+    one-shot launches of more than kOneShotMaxBlocks CTAs."""
+    # per rank: epoch word, counter, per-CTA pc (0 = not started, 1 = waiting flag0, 2 = read, 3 = counted, 4 = waiting
+    # flag1, 5 = retired); launches are sequential per rank (stream order)
+    init = (tuple(0 for _ in range(W)),                         # completed launches per rank
+            tuple(tuple(0 for _ in range(grid)) for _ in range(W)),   # CTA pcs of the running launch
+            tuple(0 for _ in range(W)),                         # counter
+            tuple(0 for _ in range(W)),                         # epoch word
+            tuple(tuple(0 for _ in range(W)) for _ in range(W)),      # flag0[r][src]
+            tuple(tuple(0 for _ in range(W)) for _ in range(W)),      # flag1[r][src]
+            tuple(tuple(0 for _ in range(grid)) for _ in range(W)))   # epoch value each CTA read at its start
+    seen, stack = {init}, [init]
+
+    def set2(t, i, v):
+        return t[:i] + (v,) + t[i + 1:]
+
+    while stack:
+        st = stack.pop()
+        done, pcs, counter, epoch_word, flag0, flag1, myep = st
+        if all(d == epochs for d in done):
+            continue
+        progressed = False
+        for r in range(W):
+            if done[r] == epochs:
+                continue
+            peers = [p for p in range(W) if p != r]
+            live = sum(1 for pc in pcs[r] if 0 < pc < 5)
+            for c in range(grid):
+                pc = pcs[r][c]
+                nxt = None
+                if pc == 0 and live < resident and (c == 0 or pcs[r][c - 1] > 0):      # CTAs start in index order
+                    e = epoch_word[r] + 1
+                    f0 = flag0
+                    if c == 0:                                                        # block 0 announces
+                        for p in peers:
+                            f0 = set2(f0, p, set2(f0[p], r, e))
+                    nxt = (done, set2(pcs, r, set2(pcs[r], c, 1)), counter, epoch_word, f0, flag1,
+                           set2(myep, r, set2(myep[r], c, e)))
+                elif pc == 1 and all(flag0[r][p] >= myep[r][c] for p in peers):
+                    nxt = (done, set2(pcs, r, set2(pcs[r], c, 2)), counter, epoch_word, flag0, flag1, myep)
+                elif pc == 2:                                                          # read done -> count
+                    last = counter[r] == grid - 1
+                    cnt = 0 if last else counter[r] + 1
+                    ew, f1 = epoch_word, flag1
+                    if last:
+                        if myep[r][c] != epoch_word[r] + 1:
+                            return "rank %d: CTAs of one launch disagree about the epoch" % r, len(seen)
+                        ew = set2(epoch_word, r, myep[r][c])
+                        for p in peers:
+                            f1 = set2(f1, p, set2(f1[p], r, myep[r][c]))
+                    nxt = (done, set2(pcs, r, set2(pcs[r], c, 4)), set2(counter, r, cnt), ew, flag0, f1, myep)
+                elif pc == 4 and all(flag1[r][p] >= myep[r][c] for p in peers):
+                    npcs = set2(pcs[r], c, 5)
+                    nd = done
+                    if all(x == 5 for x in npcs):                                      # launch retired: next one may start
+                        nd = set2(done, r, done[r] + 1)
+                        npcs = tuple(0 for _ in range(grid))
+                    nxt = (nd, set2(pcs, r, npcs), counter, epoch_word, flag0, flag1, myep)
+                if nxt is not None:
+                    progressed = True
+                    if nxt not in seen:
+                        seen.add(nxt)
+                        stack.append(nxt)
+        if not progressed:
+            return "deadlock: CTA states %s" % (pcs,), len(seen)
+    return None, len(seen)
+
+
 DROPS = ("join", "rs_wait", "tail_wait", "tail_done", "adam_round")
 DROPS_PIPELINED = DROPS + ("need",)
 
@@ -290,6 +367,9 @@ def main():
         for d in (DROPS_PIPELINED if pipelined else DROPS):
             v, n = check(W, B, T, drop=d, pipelined=pipelined)
             print("  without %-11s: %s (%d states)" % (d, v or "NO VIOLATION FOUND", n))
+    for grid, resident in ((3, 3), (4, 3)):
+        v, n = check_one_shot(W, grid, resident)
+        print("one-shot kernel, %d CTAs, %d co-resident: %s (%d states)" % (grid, resident, v or "no deadlock in any interleaving", n))
 
 
 if __name__ == "__main__":

@@ -220,7 +220,8 @@ def _spawn_supervised(args, nprocs, spawn_args, fresh_port=False):
     checkpoint carries the iterator position, the schedule and the update count, so the run continues where the last
     checkpoint left it).  The reference has no recovery path: a dead rank hangs the job until the scheduler kills it.
     On several nodes every node's launcher sees its own ranks fail (collective error, or the peer-to-peer watchdog,
-    exit code 86) and restarts them; they meet again at the same ``--distributed-init-method``."""
+    exit code 86) and restarts them towards the same ``--distributed-init-method`` (only the single-node case is
+    covered by a test)."""
     from torch.multiprocessing import ProcessExitedException, ProcessRaisedException
     attempt = 0
     while True:

@@ -195,6 +195,6 @@ def build_progress_bar(args, iterator, epoch=None, prefix=None, default="simple"
     else:
         raise ValueError("Unknown log format: {}".format(fmt))
     jsonl = getattr(args, "log_jsonl", None)
-    if jsonl:
+    if jsonl and (getattr(args, "distributed_rank", 0) or 0) == 0:      # one writer: the master rank, like the text log
         bar = tee_progress_bar(bar, json_progress_bar(iterator, epoch, prefix, interval, path=jsonl))
     return bar

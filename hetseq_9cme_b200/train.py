@@ -178,6 +178,8 @@ def validate(args, controller, task, epoch_itr, subsets):
         stats["num_updates"] = controller.get_num_updates()
         print("| epoch {:03d} | valid on '{}' subset | loss {:.3f} | ppl {} | num_updates {}".format(
             epoch_itr.epoch, subset, meter.avg, stats["ppl"], stats["num_updates"]), flush=True)
+        if getattr(args, "log_jsonl", None) and distributed_utils.is_master(args):
+            progress_bar.json_progress_bar([], epoch_itr.epoch, path=args.log_jsonl).print(stats, tag="valid/" + subset)
         losses.append(meter.avg if meter.count > 0 else None)
     return losses or [None]
 

@@ -403,3 +403,24 @@ def test_sharded_step_protocol_has_no_race_in_any_interleaving():
     # kOneShotMaxBlocks guard in b200_p2p_allreduce)
     assert pm.check_one_shot(2, 3, 3)[0] is None and pm.check_one_shot(3, 2, 2)[0] is None
     assert "deadlock" in pm.check_one_shot(2, 4, 3)[0]
+
+
+def test_jsonl_sink_mirrors_the_training_log(tmp_path):
+    """--log-jsonl: every logged step and the end-of-epoch summaries as JSON lines with the reference's stat names
+    (SURVEY §5.5 "optional JSONL sink"), next to the unchanged text log."""
+    import json
+    from hetseq_9cme_b200 import options, train
+    from hetseq_9cme_b200.data import synthetic
+    d = str(tmp_path)
+    synthetic.make_mnist(d, 16 * 4, 32)
+    path = os.path.join(d, "log.jsonl")
+    argv = ["--task", "mnist", "--optimizer", "adadelta", "--data", d, "--cpu", "--max-sentences", "16", "--lr", "1.0",
+            "--valid-subset", "test", "--save-dir", os.path.join(d, "ckpt"), "--distributed-world-size", "1", "--num-workers", "0",
+            "--clip-norm", "100", "--log-format", "simple", "--log-interval", "1", "--max-epoch", "1", "--no-save", "--seed", "3",
+            "--log-jsonl", path]
+    train.main(options.parse_training_args(argv))
+    recs = [json.loads(line) for line in open(path)]
+    steps = [r for r in recs if "update" in r]
+    assert len(steps) >= 3 and all({"loss", "ppl", "wps", "ups", "num_updates", "lr", "gnorm", "clip"} <= set(r) for r in steps)
+    assert [r["num_updates"] for r in steps] == sorted(r["num_updates"] for r in steps)
+    assert any(r.get("tag") == "train" for r in recs) and any("valid" in str(r.get("tag")) for r in recs)

@@ -347,7 +347,8 @@ class _Optimizer:
         return self.optimizer.state_dict()
 
     def load_state_dict(self, state_dict, optimizer_overrides=None):
-        """Loads state but keeps *this* run's hyper-parameters unless overridden (ref: hetseq/optim.py:39-53)."""
+        """Loads state and hyper-parameters from the checkpoint, then applies ``--optimizer-overrides`` to every group
+        (ref: hetseq/optim.py:39-53; scheduled values such as lr are set again by the scheduler's next update)."""
         self.optimizer.load_state_dict(state_dict)
         if optimizer_overrides:
             for group in self.optimizer.param_groups:

@@ -424,3 +424,63 @@ def test_jsonl_sink_mirrors_the_training_log(tmp_path):
     assert len(steps) >= 3 and all({"loss", "ppl", "wps", "ups", "num_updates", "lr", "gnorm", "clip"} <= set(r) for r in steps)
     assert [r["num_updates"] for r in steps] == sorted(r["num_updates"] for r in steps)
     assert any(r.get("tag") == "train" for r in recs) and any("valid" in str(r.get("tag")) for r in recs)
+
+
+def _mnist_cli(tmp, name, extra, data):
+    """One `train.main` run on synthetic MNIST; returns (controller, captured stdout, save dir)."""
+    import contextlib
+    import io
+    from hetseq_9cme_b200 import options, train
+    save = os.path.join(tmp, name)
+    argv = ["--task", "mnist", "--optimizer", "adadelta", "--data", data, "--cpu", "--max-sentences", "16", "--lr", "1.0",
+            "--valid-subset", "test", "--save-dir", save, "--distributed-world-size", "1", "--num-workers", "0",
+            "--clip-norm", "100", "--log-format", "simple", "--log-interval", "100", "--seed", "3"] + extra
+    buf = io.StringIO()
+    with contextlib.redirect_stdout(buf):
+        c = train.main(options.parse_training_args(argv))
+    return c, buf.getvalue(), save
+
+
+def test_checkpoint_and_schedule_flags_behave_like_the_reference(tmp_path):
+    """The resume / checkpoint-policy / stopping flags of hetseq/options.py:238-349, end to end through train.main:
+    --reset-* and --optimizer-overrides on resume, --max-update, --min-lr, --validate-interval, --disable-validation,
+    --no-epoch-checkpoints, --no-last-checkpoints, --no-save-optimizer-state, --keep-last-epochs, a per-epoch
+    --update-freq list, --max-tokens batching."""
+    from hetseq_9cme_b200.data import synthetic
+    tmp = str(tmp_path)
+    data = os.path.join(tmp, "data")
+    synthetic.make_mnist(data, 16 * 6, 32)                      # 6 batches of 16 per epoch
+
+    c, out, save = _mnist_cli(tmp, "a", ["--max-epoch", "2"], data)
+    assert c.get_num_updates() == 12
+    assert sorted(os.listdir(save)) == ["checkpoint1.pt", "checkpoint2.pt", "checkpoint_best.pt", "checkpoint_last.pt"]
+    # plain resume continues at epoch 3; with every --reset flag the weights are kept but counting starts over
+    c, out, _ = _mnist_cli(tmp, "a", ["--max-epoch", "3"], data)
+    assert "(epoch 2 @ 12 updates)" in out and c.get_num_updates() == 18
+    c, out, _ = _mnist_cli(tmp, "a", ["--max-epoch", "1", "--reset-optimizer", "--reset-lr-scheduler", "--reset-meters",
+                                      "--reset-dataloader"], data)
+    assert "@ 0 updates)" in out and c.get_num_updates() == 6
+    c, out, _ = _mnist_cli(tmp, "a", ["--max-epoch", "2", "--optimizer-overrides", "{'rho': 0.5}"], data)
+    assert c.optimizer.optimizer.param_groups[0]["rho"] == 0.5
+
+    c, out, save = _mnist_cli(tmp, "b", ["--max-epoch", "10", "--max-update", "5"], data)
+    assert c.get_num_updates() == 5
+    c, out, _ = _mnist_cli(tmp, "c", ["--max-epoch", "5", "--min-lr", "2.0"], data)
+    assert c.get_num_updates() == 0                                    # lr 1.0 is already below --min-lr
+    c, out, _ = _mnist_cli(tmp, "d", ["--max-epoch", "2", "--validate-interval", "2"], data)
+    assert out.count("valid on 'test'") == 1 and "epoch 002 | valid" in out
+    c, out, _ = _mnist_cli(tmp, "e", ["--max-epoch", "1", "--disable-validation"], data)
+    assert "valid on" not in out
+
+    c, out, save = _mnist_cli(tmp, "f", ["--max-epoch", "2", "--no-epoch-checkpoints", "--no-save-optimizer-state"], data)
+    assert sorted(os.listdir(save)) == ["checkpoint_best.pt", "checkpoint_last.pt"]
+    assert "last_optimizer_state" not in torch.load(os.path.join(save, "checkpoint_last.pt"), weights_only=False)
+    c, out, save = _mnist_cli(tmp, "g", ["--max-epoch", "2", "--no-last-checkpoints"], data)
+    assert "checkpoint_last.pt" not in os.listdir(save) and "checkpoint2.pt" in os.listdir(save)
+    c, out, save = _mnist_cli(tmp, "h", ["--max-epoch", "3", "--keep-last-epochs", "1"], data)
+    assert sorted(os.listdir(save)) == ["checkpoint3.pt", "checkpoint_best.pt", "checkpoint_last.pt"]
+
+    c, out, _ = _mnist_cli(tmp, "i", ["--max-epoch", "2", "--update-freq", "2,1"], data)
+    assert c.get_num_updates() == 3 + 6                                # epoch 1 accumulates two batches per update
+    c, out, _ = _mnist_cli(tmp, "j", ["--max-epoch", "1", "--max-tokens", "8"], data)
+    assert c.get_num_updates() == 12                                   # one "token" per image: batches of 8

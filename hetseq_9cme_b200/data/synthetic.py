@@ -99,38 +99,44 @@ def make_mnist(root: str, n_train: int = 2048, n_test: int = 512, seed: int = 0)
 CONLL_TAGS = ["O", "B-PER", "I-PER", "B-ORG", "I-ORG", "B-LOC", "I-LOC", "B-MISC", "I-MISC"]
 
 
-def make_conll(root: str, n_train: int = 256, n_valid: int = 64, n_test: int = 64, vocab_words: int = 500, seed: int = 0):
-    """CoNLL-2003-shaped files: ``token POS chunk NER`` per line, blank line between sentences; plus vocab.txt."""
+def make_conll(root: str, n_train: int = 256, n_valid: int = 64, n_test: int = 64, vocab_words: int = 500, seed: int = 0,
+               entities: int = 0, entity_dim: int = 16):
+    """CoNLL-2003-shaped files: ``token POS chunk NER`` per line, blank line between sentences; plus vocab.txt.
+    ``entities > 0`` adds what the entity-linking task reads: a fifth column with the linked entity's name (``O`` when
+    unlinked), ``entity_vocab.txt`` (line number = id, id 0 = no entity) and ``ent_vecs.pt`` ([entities + 1, entity_dim])."""
     rng = np.random.RandomState(seed)
     os.makedirs(root, exist_ok=True)
     words = ["w%d" % i for i in range(vocab_words)]
 
     def sentence():
         n = rng.randint(4, 40)
-        toks, tags = [], []
+        toks, tags, ents = [], [], []
         i = 0
         while i < n:
             if rng.rand() < 0.15:
                 kind = rng.choice(["PER", "ORG", "LOC", "MISC"])
                 ln = rng.randint(1, 4)
+                ent = "E%d" % rng.randint(1, entities + 1) if entities else "O"
                 for j in range(ln):
                     toks.append(words[rng.randint(vocab_words // 2, vocab_words)])
                     tags.append(("B-" if j == 0 else "I-") + kind)
+                    ents.append(ent)
                 i += ln
             else:
                 toks.append(words[rng.randint(0, vocab_words // 2)])
                 tags.append("O")
+                ents.append("O")
                 i += 1
-        return toks, tags
+        return toks, tags, ents
 
     def write(name, n):
         path = os.path.join(root, name)
         with open(path, "w") as f:
             f.write("-DOCSTART- -X- -X- O\n\n")
             for _ in range(n):
-                toks, tags = sentence()
-                for t, g in zip(toks, tags):
-                    f.write("%s NN B-NP %s\n" % (t, g))
+                toks, tags, ents = sentence()
+                for t, g, e in zip(toks, tags, ents):
+                    f.write("%s NN B-NP %s%s\n" % (t, g, (" " + e) if entities else ""))
                 f.write("\n")
         return path
 
@@ -140,4 +146,12 @@ def make_conll(root: str, n_train: int = 256, n_valid: int = 64, n_test: int = 6
         for t in ["[PAD]", "[UNK]", "[CLS]", "[SEP]", "[MASK]"] + words:
             f.write(t + "\n")
     paths["vocab"] = vocab
+    if entities:
+        import torch
+        with open(os.path.join(root, "entity_vocab.txt"), "w") as f:
+            for name in ["O"] + ["E%d" % k for k in range(1, entities + 1)]:
+                f.write(name + "\n")
+        vecs = torch.from_numpy(rng.randn(entities + 1, entity_dim).astype(np.float32))
+        paths["ent_vecs"] = os.path.join(root, "ent_vecs.pt")
+        torch.save(vecs, paths["ent_vecs"])
     return paths

@@ -1,5 +1,6 @@
 """Model-level parity on CPU: state-dict keys and losses against the reference BERT file, datasets, collators,
 NER pipeline, and a tiny BERT pre-training run through the CLI."""
+import math
 import os
 import sys
 import types
@@ -250,3 +251,32 @@ def test_packed_batches_assemble_to_the_same_tensors(tmp_path):
     raw[0, 28:32] = torch.tensor([11, 12, 13, 14])
     labels = assemble_host(raw, 8, 4)[3][0].tolist()
     assert labels == [-1, -1, -1, -1, -1, 12, -1, -1]
+
+
+def test_entity_linking_task_trains_end_to_end(tmp_path):
+    """`--task BertForELClassification` (hetseq/tasks/bert_for_el_classification_task.py, hetseq/model/
+    bert_for_EL_classification.py; the reference's smoke script is test/test_entity_vocab/test_CONLL_2003_EL.py): CoNLL
+    files with an entity column, entity vectors from --ent_vecs_filename, the joint token-classification + cosine
+    entity loss through train.main; both losses are finite and fall, the frozen entity table stays untouched."""
+    from hetseq_9cme_b200 import options, train
+    from hetseq_9cme_b200.data import synthetic
+    d = str(tmp_path)
+    paths = synthetic.make_conll(d, n_train=64, n_valid=8, n_test=8, vocab_words=60, entities=5, entity_dim=12)
+    cfg = synthetic.write_bert_config(os.path.join(d, "c.json"), vocab_size=65, **CFG)
+    vecs = torch.load(paths["ent_vecs"])
+    argv = ["--task", "BertForELClassification", "--optimizer", "adam", "--data", d, "--dict", paths["vocab"], "--config_file", cfg,
+            "--train_file", paths["train"], "--validation_file", paths["validation"], "--test_file", paths["test"],
+            "--ent_vecs_filename", paths["ent_vecs"], "--cpu", "--max-sentences", "8", "--lr", "3e-3", "--valid-subset", "test",
+            "--save-dir", d + "/ck", "--max-epoch", "1", "--distributed-world-size", "1", "--num-workers", "0", "--log-format", "none"]
+    torch.manual_seed(0)
+    c = train.main(options.parse_training_args(argv))
+    model = c.get_model()
+    assert type(model).__name__ == "BertForELClassification" and c.get_num_updates() == 8
+    ner0, ent0 = (float(x) for x in model.last_losses)
+    c = train.main(options.parse_training_args(argv[:argv.index("--max-epoch") + 1] + ["4"] + argv[argv.index("--max-epoch") + 2:]))
+    ner1, ent1 = (float(x) for x in c.get_model().last_losses)
+    assert all(math.isfinite(v) for v in (ner0, ent0, ner1, ent1)) and ner1 < ner0 and ent1 < ent0
+    sd = torch.load(d + "/ck/checkpoint_last.pt", weights_only=False)["model"]
+    assert torch.equal(sd["entity_emb.weight"], vecs) and sd["entity_classifier.weight"].shape == (12, CFG["hidden_size"])
+    feats = c.task.dataset("train")[0] if hasattr(c.task.dataset("train"), "__getitem__") else None
+    assert feats is not None and "entity_labels" in feats and max(feats["entity_labels"]) <= 5

@@ -280,3 +280,22 @@ def test_entity_linking_task_trains_end_to_end(tmp_path):
     assert torch.equal(sd["entity_emb.weight"], vecs) and sd["entity_classifier.weight"].shape == (12, CFG["hidden_size"])
     feats = c.task.dataset("train")[0] if hasattr(c.task.dataset("train"), "__getitem__") else None
     assert feats is not None and "entity_labels" in feats and max(feats["entity_labels"]) <= 5
+
+
+@pytest.mark.parametrize("compress,chunk_rows", [(False, 1024), (True, 4), (True, 1024)])
+def test_hdf5_lite_round_trip(tmp_path, compress, chunk_rows):
+    """The built-in HDF5 reader / writer (data/hdf5_lite.py — the image has no h5py / libhdf5): contiguous and chunked +
+    gzip layouts, the integer widths NVIDIA's BERT shards use, a chunk size that does not divide the row count."""
+    from hetseq_9cme_b200.data import hdf5_lite
+    rng = np.random.RandomState(0)
+    arrs = {"input_ids": rng.randint(0, 30000, (37, 128)).astype(np.int32),
+            "input_mask": rng.randint(0, 2, (37, 128)).astype(np.int8),
+            "next_sentence_labels": rng.randint(0, 2, (37,)).astype(np.int8),
+            "masked_lm_ids": rng.randint(0, 30000, (37, 20)).astype(np.int64)}
+    path = str(tmp_path / "shard.hdf5")
+    hdf5_lite.write_hdf5(path, arrs, compress=compress, chunk_rows=chunk_rows)
+    back = hdf5_lite.read_hdf5(path)
+    assert set(back) == set(arrs)
+    for k, v in arrs.items():
+        assert back[k].dtype == v.dtype and np.array_equal(back[k], v), k
+    assert open(path, "rb").read(8) == b"\\x89HDF\\r\\n\\x1a\\n"           # a real HDF5 signature: h5py / h5dump can open it

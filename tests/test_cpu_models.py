@@ -298,4 +298,4 @@ def test_hdf5_lite_round_trip(tmp_path, compress, chunk_rows):
     assert set(back) == set(arrs)
     for k, v in arrs.items():
         assert back[k].dtype == v.dtype and np.array_equal(back[k], v), k
-    assert open(path, "rb").read(8) == b"\\x89HDF\\r\\n\\x1a\\n"           # a real HDF5 signature: h5py / h5dump can open it
+    assert open(path, "rb").read(8) == b"\x89HDF\r\n\x1a\n"           # a real HDF5 signature: h5py / h5dump can open it

@@ -299,3 +299,39 @@ def test_hdf5_lite_round_trip(tmp_path, compress, chunk_rows):
     for k, v in arrs.items():
         assert back[k].dtype == v.dtype and np.array_equal(back[k], v), k
     assert open(path, "rb").read(8) == b"\x89HDF\r\n\x1a\n"           # a real HDF5 signature: h5py / h5dump can open it
+
+
+def test_file_cache_and_shard_conversion(tmp_path):
+    """`file_utils.cached_path` (hetseq/file_utils.py:78-105 without the download half: local paths, file:// URLs, a
+    pre-populated cache; remote URLs that are not cached fail with a message instead of reaching for the network) and
+    `shard_io.convert_to_b2shard` (HDF5 shard -> memory-mappable shard with identical content)."""
+    from hetseq_9cme_b200 import file_utils
+    from hetseq_9cme_b200.data import shard_io, synthetic
+    d = str(tmp_path)
+    local = os.path.join(d, "archive.bin")
+    open(local, "wb").write(b"x")
+    assert file_utils.cached_path(local) == local and file_utils.cached_path("file://" + local) == local
+    with pytest.raises(EnvironmentError):
+        file_utils.cached_path(os.path.join(d, "missing.bin"))
+    url = "https://example.org/bert-base-uncased.tar.gz"
+    cache = os.path.join(d, "cache")
+    os.makedirs(cache)
+    with pytest.raises(EnvironmentError, match="never downloads"):
+        file_utils.cached_path(url, cache_dir=cache)
+    name = file_utils.url_to_filename(url, etag="abc")
+    open(os.path.join(cache, name), "wb").write(b"y")
+    import json
+    json.dump({"url": url, "etag": "abc"}, open(os.path.join(cache, name + ".json"), "w"))
+    assert file_utils.cached_path(url, cache_dir=cache) == os.path.join(cache, name)
+    assert file_utils.filename_to_url(name, cache_dir=cache) == (url, "abc")
+    with pytest.raises(ValueError):
+        file_utils.cached_path("ftp://example.org/x")
+
+    synthetic.make_bert_shards(d + "/h5", n_train_files=1, samples_per_file=6, seq_len=32, max_pred=5, vocab_size=2000, fmt="hdf5", test_samples=2)
+    src = os.path.join(d, "h5", "train_shard_0.hdf5")
+    dst = os.path.join(d, "train_shard_0.b2s")
+    shard_io.convert_to_b2shard(src, dst)
+    a, b = shard_io.open_shard(src), shard_io.open_shard(dst)
+    assert set(a.keys()) == set(b.keys())
+    for k in a.keys():
+        assert np.array_equal(np.asarray(a[k]), np.asarray(b[k])), k

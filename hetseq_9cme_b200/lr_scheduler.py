@@ -80,8 +80,12 @@ class PolynomialDecayScheduler(_LRScheduler):
         return self.optimizer.get_lr()
 
 
+# name (value of --lr-scheduler) -> class; extensions add theirs here and their flags to options._SCHED_ROWS
+SCHEDULER_REGISTRY = {"PolynomialDecayScheduler": PolynomialDecayScheduler}
+
+
 def build_lr_scheduler(args, optimizer):
     name = getattr(args, "lr_scheduler", "PolynomialDecayScheduler")
-    if name == "PolynomialDecayScheduler":
-        return PolynomialDecayScheduler(args, optimizer)
-    raise ValueError("unsupported lr_scheduler: {}".format(name))
+    if name not in SCHEDULER_REGISTRY:
+        raise ValueError("unsupported lr_scheduler: {}".format(name))
+    return SCHEDULER_REGISTRY[name](args, optimizer)

@@ -447,10 +447,12 @@ class _Adadelta(_Optimizer):
                 "weight_decay": getattr(self.args, "dadelta_weight_decay", 0.0)}
 
 
+# name (value of --optimizer) -> wrapper class; extensions add theirs here and their flags to options._OPT_ROWS
+OPTIMIZER_REGISTRY = {"adam": _Adam, "adadelta": _Adadelta}
+
+
 def build_optimizer(args, params):
     name = getattr(args, "optimizer", "adam")
-    if name == "adam":
-        return _Adam(args, params)
-    if name == "adadelta":
-        return _Adadelta(args, params)
-    raise ValueError("unsupported optimizer: {}".format(name))
+    if name not in OPTIMIZER_REGISTRY:
+        raise ValueError("unsupported optimizer: {}".format(name))
+    return OPTIMIZER_REGISTRY[name](args, params)

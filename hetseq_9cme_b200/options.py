@@ -309,10 +309,11 @@ def preparse(argv: Optional[Sequence[str]] = None):
     """Stage one: find ``--task/--optimizer/--lr-scheduler`` so the full flag set can be built
     (ref: hetseq/train.py:204-212)."""
     pre = argparse.ArgumentParser(add_help=False, allow_abbrev=False)
-    pre.add_argument("--task", default="bert", choices=list(TASKS))
-    pre.add_argument("--optimizer", default="adam", choices=list(OPTIMIZERS))
+    # choices come from the flag tables, so an extension that adds its rows (docs/extending.md) is accepted here too
+    pre.add_argument("--task", default="bert", choices=list(_TASK_ROWS))
+    pre.add_argument("--optimizer", default="adam", choices=list(_OPT_ROWS))
     pre.add_argument("--lr-scheduler", "--lr_scheduler", dest="lr_scheduler", default="PolynomialDecayScheduler",
-                     choices=list(LR_SCHEDULERS))
+                     choices=list(_SCHED_ROWS))
     known, _ = pre.parse_known_args(argv)
     return known
 

@@ -484,3 +484,89 @@ def test_checkpoint_and_schedule_flags_behave_like_the_reference(tmp_path):
     assert c.get_num_updates() == 3 + 6                                # epoch 1 accumulates two batches per update
     c, out, _ = _mnist_cli(tmp, "j", ["--max-epoch", "1", "--max-tokens", "8"], data)
     assert c.get_num_updates() == 12                                   # one "token" per image: batches of 8
+
+
+def test_extension_contract_new_task_dataset_model_scheduler(tmp_path):
+    """docs/extending.md (the reference's docs/source/extending.rst): a task, a dataset, a model and an LR scheduler
+    written OUTSIDE the package, registered through the public tables, trained by the unmodified `train.main` — arena,
+    fused step, checkpoints and all."""
+    import torch.nn as nn
+    from hetseq_9cme_b200 import lr_scheduler, options, tasks, train
+    from hetseq_9cme_b200.tasks import Task
+
+    class LineDataset(torch.utils.data.Dataset):
+        """y = 3 x0 - 2 x1 + 1 with a little noise."""
+
+        def __init__(self, n, seed):
+            g = torch.Generator().manual_seed(seed)
+            self.x = torch.randn(n, 2, generator=g)
+            self.y = 3 * self.x[:, 0] - 2 * self.x[:, 1] + 1 + 0.01 * torch.randn(n, generator=g)
+
+        def __len__(self):
+            return len(self.x)
+
+        def __getitem__(self, i):
+            return self.x[i], self.y[i]
+
+        def ordered_indices(self):
+            return np.arange(len(self))
+
+        def num_tokens(self, i):
+            return 1
+
+        def collater(self, samples):
+            if len(samples) == 0:
+                return None
+            return [torch.stack([s[0] for s in samples]), torch.stack([s[1] for s in samples])]
+
+        def set_epoch(self, epoch):
+            pass
+
+    class LineModel(nn.Module):
+        def __init__(self):
+            super().__init__()
+            self.lin = nn.Linear(2, 1)
+
+        def forward(self, x, y):
+            return ((self.lin(x).squeeze(-1) - y) ** 2).mean()
+
+    class LineTask(Task):
+        def load_dataset(self, split, **kwargs):
+            self.datasets[split] = LineDataset(self.args.line_samples, seed=0 if split == "train" else 1)
+
+        def build_model(self, args):
+            return LineModel()
+
+        def _sample_size(self, sample):
+            return 1                                   # the loss is already a mean
+
+    class HalvingScheduler(lr_scheduler._LRScheduler):
+        """lr = base / 2**(epoch // 4)."""
+
+        def step(self, epoch, val_loss=None):
+            super().step(epoch, val_loss)
+            self.optimizer.set_lr(self.args.lr[0] / (2 ** (epoch // 4)) * self.args.halving_scale)
+            return self.optimizer.get_lr()
+
+    tasks.TASK_REGISTRY["line"] = LineTask
+    options._TASK_ROWS["line"] = [(("--line-samples",), dict(type=int, default=64))]
+    lr_scheduler.SCHEDULER_REGISTRY["halving"] = HalvingScheduler
+    options._SCHED_ROWS["halving"] = [(("--lr_scheduler", "--lr-scheduler"), dict(default="halving", type=str)),
+                                      (("--halving-scale",), dict(type=float, default=1.0))]
+    try:
+        argv = ["--task", "line", "--line-samples", "128", "--optimizer", "adam", "--lr-scheduler", "halving", "--halving-scale", "1.0",
+                "--lr", "0.2", "--cpu", "--max-sentences", "16", "--valid-subset", "valid", "--save-dir", str(tmp_path / "ck"),
+                "--distributed-world-size", "1", "--num-workers", "0", "--log-format", "none", "--max-epoch", "8", "--clip-norm", "0",
+                "--no-epoch-checkpoints"]
+        args = options.parse_training_args(argv)
+        assert args.line_samples == 128 and args.halving_scale == 1.0
+        c = train.main(args)
+        w = c.get_model().lin.weight.detach().flatten().tolist()
+        assert abs(w[0] - 3) < 0.2 and abs(w[1] + 2) < 0.2 and abs(float(c.get_model().lin.bias) - 1) < 0.2
+        assert c.get_num_updates() == 8 * 8 and c.get_lr() == pytest.approx(0.2 / 2 ** 2)
+        assert os.path.exists(str(tmp_path / "ck" / "checkpoint_last.pt")) and c.get_meter("valid_loss").avg < 0.1
+    finally:
+        tasks.TASK_REGISTRY.pop("line", None)
+        options._TASK_ROWS.pop("line", None)
+        lr_scheduler.SCHEDULER_REGISTRY.pop("halving", None)
+        options._SCHED_ROWS.pop("halving", None)

@@ -331,7 +331,7 @@ extern "C" int b200_comm_init(int rank, int world, const char* tag, int timeout_
   return 0;
 }
 
-// Control-plane self-test, no GPU needed (tests/test_native_host.py runs it with three processes): rendezvous, an
+// Control-plane self-test, no GPU needed (tests/test_cpu_distributed.py runs it with three processes): rendezvous, an
 // AND-agreement round, one descriptor per rank passed to every peer as SCM_RIGHTS (a memfd holding a known
 // word, read back through the received descriptor), and two rounds with one rank lagging, so that a message of
 // the next round can arrive before the current one is complete (the stash).

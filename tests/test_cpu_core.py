@@ -136,11 +136,15 @@ def test_meters_roundtrip():
 def test_batch_by_size_matches_reference_cython():
     from hetseq_9cme_b200.data import data_utils
     ref_fast = None
-    try:
-        sys.path.insert(0, os.path.join(os.path.dirname(os.path.dirname(__file__)), "baseline", "_ref"))
-        from hetseq.data.data_utils_fast import batch_by_size_fast as ref_fast  # built by the baseline install
-    except Exception:
-        ref_fast = None
+    base = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "baseline")
+    if os.path.isdir(os.path.join(base, "_ref", "hetseq")):
+        # the package import pulls in h5py / boto3, which the image lacks: the baseline's stand-ins provide them
+        sys.path[:0] = [os.path.join(base, "_ref"), os.path.join(base, "shims")]
+        try:
+            from hetseq.data.data_utils_fast import batch_by_size_fast as ref_fast  # built by the baseline install
+        finally:
+            del sys.path[:2]
+        assert ref_fast is not None
     rng = np.random.RandomState(0)
     for _ in range(60):
         n = int(rng.randint(1, 300))

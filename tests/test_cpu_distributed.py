@@ -140,3 +140,35 @@ def test_dead_rank_is_restarted_from_the_last_checkpoint(tmp_path):
     cmd2[cmd2.index("--save-dir") + 1] = os.path.join(d, "ckpt2")
     r2 = subprocess.run(cmd2, capture_output=True, text=True, timeout=600, cwd=ROOT)
     assert r2.returncode != 0
+
+
+def test_heterogeneous_nodes_one_command_per_node(tmp_path):
+    """The reference's launch model for nodes with different GPU counts (docs/source/distribute.rst, the `*_het` job
+    scripts): one command per node, each with its own --distributed-gpus and the rank of its first process.  Here
+    "node 0" brings two ranks and "node 1" one, on CPUs with gloo; all three meet at the same tcp:// init method."""
+    import subprocess
+    from hetseq_9cme_b200.data import synthetic
+    from hetseq_9cme_b200.distributed_utils import find_free_port
+    d = str(tmp_path)
+    synthetic.make_mnist(d, 16 * 6, 32)                          # 6 batches over 3 ranks -> 2 updates
+    port = find_free_port()
+    common = [sys.executable, os.path.join(ROOT, "hetseq_9cme_b200", "train.py"), "--task", "mnist", "--optimizer", "adadelta",
+              "--data", d, "--cpu", "--distributed-backend", "gloo", "--distributed-init-method", "tcp://127.0.0.1:%d" % port,
+              "--distributed-world-size", "3", "--max-sentences", "16", "--lr", "1.0", "--valid-subset", "test", "--num-workers", "0",
+              "--clip-norm", "100", "--log-format", "none", "--max-epoch", "1", "--seed", "3"]
+    node0 = subprocess.Popen(common + ["--distributed-gpus", "2", "--distributed-rank", "0", "--save-dir", os.path.join(d, "ck0")],
+                             stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, cwd=ROOT)
+    node1 = subprocess.Popen(common + ["--distributed-gpus", "1", "--distributed-rank", "2", "--save-dir", os.path.join(d, "ck1")],
+                             stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, cwd=ROOT)
+    try:
+        out0, _ = node0.communicate(timeout=300)
+        out1, _ = node1.communicate(timeout=300)
+    finally:
+        for p in (node0, node1):
+            if p.poll() is None:
+                p.kill()
+    assert node0.returncode == 0 and node1.returncode == 0, out0[-2000:] + out1[-2000:]
+    assert "initialized host" in out1 and "as rank 2" in out1
+    last = torch.load(os.path.join(d, "ck0", "checkpoint_last.pt"), map_location="cpu", weights_only=False)
+    assert last["optimizer_history"][-1]["num_updates"] == 2 and last["args"].distributed_world_size == 3
+    assert not os.path.exists(os.path.join(d, "ck1", "checkpoint_last.pt"))      # only the master rank writes

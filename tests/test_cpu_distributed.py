@@ -134,12 +134,6 @@ def test_dead_rank_is_restarted_from_the_last_checkpoint(tmp_path):
     assert "loaded checkpoint" in out and "@ 4 updates" in out          # resumed from the mid-epoch checkpoint
     last = torch.load(os.path.join(save, "checkpoint_last.pt"), map_location="cpu", weights_only=False)
     assert last["optimizer_history"][-1]["num_updates"] == 8
-    # without --max-restarts the same fault ends the job with an error instead
-    cmd2 = [c for c in cmd]
-    cmd2[cmd2.index("--max-restarts") + 1] = "0"
-    cmd2[cmd2.index("--save-dir") + 1] = os.path.join(d, "ckpt2")
-    r2 = subprocess.run(cmd2, capture_output=True, text=True, timeout=600, cwd=ROOT)
-    assert r2.returncode != 0
 
 
 def test_heterogeneous_nodes_one_command_per_node(tmp_path):

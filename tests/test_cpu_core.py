@@ -574,3 +574,32 @@ def test_extension_contract_new_task_dataset_model_scheduler(tmp_path):
         options._TASK_ROWS.pop("line", None)
         lr_scheduler.SCHEDULER_REGISTRY.pop("halving", None)
         options._SCHED_ROWS.pop("halving", None)
+
+
+def test_our_mnist_checkpoint_loads_into_the_reference_evaluator(tmp_path):
+    """'Checkpoints go both ways': a checkpoint written by this framework loads strictly into the model class of the
+    reference's own evaluation script (hetseq/eval_mnist.py:9-36, :48-51) and gives the same outputs."""
+    pytest.importorskip("torchvision")
+    ref_path = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "baseline", "_ref", "hetseq", "eval_mnist.py")
+    if not os.path.exists(ref_path):
+        ref_path = "/root/reference/hetseq/eval_mnist.py"
+    if not os.path.exists(ref_path):
+        pytest.skip("reference not available")
+    import importlib.util
+    spec = importlib.util.spec_from_file_location("ref_eval_mnist", ref_path)
+    ref = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(ref)
+    from hetseq_9cme_b200.data import synthetic
+    data = os.path.join(str(tmp_path), "data")
+    synthetic.make_mnist(data, 16 * 4, 32)
+    c, _, save = _mnist_cli(str(tmp_path), "ck", ["--max-epoch", "1"], data)
+    ckpt = torch.load(os.path.join(save, "checkpoint_last.pt"), map_location="cpu", weights_only=False)
+    net = ref.MNISTNet()
+    net.load_state_dict(ckpt["model"], strict=True)
+    net.eval()
+    ours = c.get_model().eval()
+    x, y = torch.randn(5, 1, 28, 28), torch.randint(0, 10, (5,))
+    with torch.no_grad():
+        out_ref, loss_ref = net(x, y, eval=True)
+        loss_ours = ours(x, y)
+    assert torch.allclose(loss_ref, loss_ours, atol=1e-6) and out_ref.shape == (5, 10)
